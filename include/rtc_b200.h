@@ -230,6 +230,19 @@ int rt_device_count(void);
 int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene **out);
 void rt_scene_destroy(rt_scene *scene);
 
+/* Host-only: validates `desc` and builds the rebuilt acceleration structure WITHOUT touching a device; reports its
+ * shape.  (What rt_scene_create would upload.)  Works on machines without a GPU. */
+typedef struct rt_scene_info {
+  uint32_t bvh_nodes;     /* binary nodes (each holds both children's boxes) */
+  uint32_t bvh_depth;     /* deepest traversal stack the kernels need */
+  uint32_t spheres, quads, instances, media, chain_ops;
+  uint32_t graph_frames, graph_rays, graph_recs; /* nesting of the reference-order graph (exact kernel limits) */
+  int32_t light_nesting;  /* lists under world.lights; -1 = a list nothing can be sampled from */
+  uint32_t mega_supported;
+  uint64_t device_bytes;  /* bytes rt_scene_create uploads */
+} rt_scene_info;
+int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info);
+
 /* Camera_render through HOST buffers: uploads nothing but the camera, renders samples
  * [sample_begin, sample_begin+sample_count) of every pixel, and copies back
  *   radiance_sum : float[h][w][3] per-pixel SUM over the rendered samples (may be NULL)

@@ -48,6 +48,22 @@ void rtc_synthetic_image(int width, int height, uint8_t *rgb);
 int rtc_camera_render_opts(const Camera *camera, const World *world, const rt_opts *opts, int n_gpus,
                            uint8_t *rgb8, float *radiance_sum, rt_stats *stats);
 
+/* Opaque handle around one built-in scene, for FFI callers that cannot hold World / Camera (session.c).
+ * width/spp/depth <= 0 and aspect/lights_prob < 0 keep the scene's own value. */
+typedef struct rtc_session rtc_session;
+rtc_session *rtc_session_open(int scene_id, int width, int spp, int depth, float aspect, float lights_prob);
+void rtc_session_close(rtc_session *s);
+int rtc_session_width(const rtc_session *s);
+int rtc_session_height(const rtc_session *s);
+int rtc_session_spp(const rtc_session *s);
+void rtc_session_camera(const rtc_session *s, rt_camera *out);
+size_t rtc_session_camera_raw(const rtc_session *s, void *out, size_t cap);
+int rtc_session_flatten(const rtc_session *s, rt_scene_desc *out);
+int rtc_session_write_blob(const rtc_session *s, const char *path);
+int rtc_session_render(const rtc_session *s, const rt_opts *opts, int n_gpus, uint8_t *rgb8, float *radiance_sum,
+                       rt_stats *stats);
+void rtc_session_camera_render(const rtc_session *s, uint8_t *rgb8);
+
 #ifdef __cplusplus
 }
 #endif

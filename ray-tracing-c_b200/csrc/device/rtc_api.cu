@@ -1,0 +1,655 @@
+/*
+ * rtc_api.cu -- the C ABI of librtc_b200.so (include/rtc_b200.h): scene upload, render entry points, tonemap,
+ * hit batches, single-process multi-GPU render.  No torch, no C++ types across the boundary, no CPU fallback:
+ * every compute entry point fails with RT_ERR_NO_DEVICE when there is no CUDA device.
+ */
+#include "rtc_bvh.h"
+#include "rtc_kernels.h"
+#include "rtc_graph.cuh"
+#include "rtc_trace.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+/* ------------------------------------------------------------------ errors ------------------------------- */
+
+static thread_local char g_error[512] = "";
+
+static int fail(int status, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+  return status;
+}
+#define CUDA_TRY(expr)                                                                                               \
+  do {                                                                                                               \
+    cudaError_t err__ = (expr);                                                                                      \
+    if (err__ != cudaSuccess)                                                                                        \
+      return fail(err__ == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "%s: %s", #expr,                  \
+                  cudaGetErrorString(err__));                                                                        \
+  } while (0)
+
+extern "C" const char *rt_last_error(void) { return g_error; }
+extern "C" uint32_t rt_abi_version(void) { return RT_ABI_VERSION; }
+extern "C" int rt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+/* ------------------------------------------------------------------ scene -------------------------------- */
+
+struct rt_scene {
+  int device = 0;
+  std::vector<void *> allocations;
+  DScene view;
+  BuiltScene built_info; /* limits only; the arrays are cleared after upload */
+  bool mega_ok = true;
+  std::string mega_why;
+  /* per-scene scratch reused across renders */
+  RenderCounters *counters = nullptr;
+  void *scratch = nullptr;
+  size_t scratch_bytes = 0;
+  float *radiance = nullptr;
+  size_t radiance_bytes = 0;
+  uint8_t *rgb8 = nullptr;
+  size_t rgb8_bytes = 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  rt_stats last = {};
+  int last_launches = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int previous = -1;
+  explicit DeviceGuard(int device) {
+    cudaGetDevice(&previous);
+    if (device != previous)
+      cudaSetDevice(device);
+  }
+  ~DeviceGuard() {
+    if (previous >= 0)
+      cudaSetDevice(previous);
+  }
+};
+
+template <typename T> int upload(rt_scene *s, const T *host, size_t count, const T **out) {
+  size_t bytes = (count ? count : 1) * sizeof(T);
+  void *dev = nullptr;
+  CUDA_TRY(cudaMalloc(&dev, bytes));
+  s->allocations.push_back(dev);
+  if (count)
+    CUDA_TRY(cudaMemcpy(dev, host, count * sizeof(T), cudaMemcpyHostToDevice));
+  else
+    CUDA_TRY(cudaMemset(dev, 0, bytes));
+  *out = static_cast<const T *>(dev);
+  return RT_OK;
+}
+
+int ensure(void **ptr, size_t *have, size_t need) {
+  if (*have >= need && *ptr)
+    return RT_OK;
+  if (*ptr)
+    cudaFree(*ptr);
+  *ptr = nullptr;
+  *have = 0;
+  CUDA_TRY(cudaMalloc(ptr, need ? need : 16));
+  *have = need;
+  return RT_OK;
+}
+
+} // namespace
+
+extern "C" void rt_scene_destroy(rt_scene *scene) {
+  if (!scene)
+    return;
+  DeviceGuard guard(scene->device);
+  for (void *p : scene->allocations)
+    cudaFree(p);
+  if (scene->counters)
+    cudaFree(scene->counters);
+  if (scene->scratch)
+    cudaFree(scene->scratch);
+  if (scene->radiance)
+    cudaFree(scene->radiance);
+  if (scene->rgb8)
+    cudaFree(scene->rgb8);
+  for (cudaEvent_t e : scene->ev)
+    if (e)
+      cudaEventDestroy(e);
+  delete scene;
+}
+
+extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene **out) {
+  if (!desc || !out)
+    return fail(RT_ERR_INVALID, "rt_scene_create: NULL argument");
+  *out = nullptr;
+  std::string why = rtc_validate_desc(*desc);
+  if (!why.empty())
+    return fail(RT_ERR_INVALID, "rt_scene_create: %s", why.c_str());
+  if (rt_device_count() <= 0)
+    return fail(RT_ERR_NO_DEVICE, "rt_scene_create: no CUDA device (this library does not compute on the host)");
+  if (device < 0)
+    CUDA_TRY(cudaGetDevice(&device));
+
+  BuiltScene built;
+  rtc_build_scene(*desc, built);
+  if (built.graph_frames > GRAPH_MAX_FRAMES || built.graph_rays > GRAPH_MAX_RAYS || built.graph_recs > GRAPH_MAX_RECS)
+    return fail(RT_ERR_UNSUPPORTED, "rt_scene_create: graph nesting (calls %d, instance levels %d, medium levels %d) "
+                                    "exceeds the limits %d/%d/%d",
+                built.graph_frames, built.graph_rays, built.graph_recs, GRAPH_MAX_FRAMES, GRAPH_MAX_RAYS,
+                GRAPH_MAX_RECS);
+  if (built.light_nesting < 0)
+    return fail(RT_ERR_INVALID, "rt_scene_create: a list under world.lights has no item that can be sampled");
+  if (built.light_nesting > RTC_LIGHT_NESTING)
+    return fail(RT_ERR_UNSUPPORTED, "rt_scene_create: lists nested %d deep under world.lights (limit %d)",
+                built.light_nesting, RTC_LIGHT_NESTING);
+
+  rt_scene *s = new (std::nothrow) rt_scene();
+  if (!s)
+    return fail(RT_ERR_NOMEM, "rt_scene_create: out of host memory");
+  s->device = device;
+  DeviceGuard guard(device);
+  s->mega_ok = built.mega_supported;
+  s->mega_why = built.mega_why;
+  if (s->mega_ok && built.max_stack + 2 > TRACE_STACK) {
+    s->mega_ok = false;
+    s->mega_why = "rebuilt BVH deeper than the traversal stack";
+  }
+
+  DScene &v = s->view;
+  memset(&v, 0, sizeof(v));
+  int rc = RT_OK;
+#define UP(field, host, count)                                                                                       \
+  if (rc == RT_OK)                                                                                                   \
+  rc = upload(s, host, (size_t)(count), &v.field)
+  UP(nodes, desc->nodes, desc->n_nodes);
+  UP(children, desc->children, desc->n_children);
+  UP(spheres, desc->spheres, desc->n_spheres);
+  UP(quads, desc->quads, desc->n_quads);
+  UP(materials, desc->materials, desc->n_materials);
+  UP(textures, desc->textures, desc->n_textures);
+  UP(perlins, desc->perlins, desc->n_perlins);
+  UP(images, desc->images, desc->n_images);
+  UP(texels, desc->texels, desc->n_texel_bytes);
+  UP(bnodes, built.bnodes.data(), built.bnodes.size());
+  UP(msph, built.msph.data(), built.msph.size());
+  UP(msph_meta, built.msph_meta.data(), built.msph_meta.size());
+  UP(mquads, built.mquads.data(), built.mquads.size());
+  UP(insts, built.insts.data(), built.insts.size());
+  UP(ops, built.ops.data(), built.ops.size());
+  UP(media, built.media.data(), built.media.size());
+#undef UP
+  v.objects_root = desc->objects_root;
+  v.lights_root = desc->lights_root;
+  v.world_root = built.world_root;
+  v.n_media = (uint32_t)built.media.size();
+  if (rc == RT_OK) {
+    cudaError_t err = cudaMalloc(&s->counters, sizeof(RenderCounters));
+    for (int k = 0; k < 4 && err == cudaSuccess; k++)
+      err = cudaEventCreate(&s->ev[k]);
+    if (err != cudaSuccess)
+      rc = fail(RT_ERR_CUDA, "rt_scene_create: %s", cudaGetErrorString(err));
+  }
+  if (rc != RT_OK) {
+    rt_scene_destroy(s);
+    return rc;
+  }
+  built.bnodes.clear(), built.msph.clear(), built.msph_meta.clear(), built.mquads.clear();
+  s->built_info = built;
+  *out = s;
+  return RT_OK;
+}
+
+extern "C" int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info) {
+  if (!desc || !info)
+    return fail(RT_ERR_INVALID, "rt_scene_inspect: NULL argument");
+  std::string why = rtc_validate_desc(*desc);
+  if (!why.empty())
+    return fail(RT_ERR_INVALID, "rt_scene_inspect: %s", why.c_str());
+  BuiltScene b;
+  rtc_build_scene(*desc, b);
+  memset(info, 0, sizeof(*info));
+  info->bvh_nodes = (uint32_t)b.bnodes.size();
+  info->bvh_depth = (uint32_t)b.max_stack;
+  info->spheres = (uint32_t)b.msph.size(), info->quads = (uint32_t)b.mquads.size();
+  info->instances = (uint32_t)b.insts.size(), info->media = (uint32_t)b.media.size();
+  info->chain_ops = (uint32_t)b.ops.size();
+  info->graph_frames = (uint32_t)b.graph_frames, info->graph_rays = (uint32_t)b.graph_rays;
+  info->graph_recs = (uint32_t)b.graph_recs;
+  info->light_nesting = b.light_nesting;
+  info->mega_supported = b.mega_supported && b.max_stack + 2 <= TRACE_STACK;
+  info->device_bytes = sizeof(rt_node) * desc->n_nodes + 4ull * desc->n_children + sizeof(rt_sphere) * desc->n_spheres +
+                       sizeof(rt_quad) * desc->n_quads + sizeof(rt_material) * desc->n_materials +
+                       sizeof(rt_texture) * desc->n_textures + sizeof(rt_perlin) * desc->n_perlins +
+                       sizeof(rt_image) * desc->n_images + desc->n_texel_bytes + sizeof(BNode) * b.bnodes.size() +
+                       (sizeof(MSphere) + sizeof(MPrimMeta)) * b.msph.size() + sizeof(MQuad) * b.mquads.size() +
+                       sizeof(Instance) * b.insts.size() + sizeof(ChainOp) * b.ops.size() +
+                       sizeof(MMedium) * b.media.size();
+  return RT_OK;
+}
+
+/* ------------------------------------------------------------------ tonemap ------------------------------ */
+
+/* raytracing.c:127-131 with utils.h's clamp: NaN and negatives -> 0 */
+__global__ void tonemap_kernel(const float *__restrict__ sum, size_t n, float spp, uint8_t *__restrict__ rgb8) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  float v = __fsqrt_rn(__fdiv_rn(sum[i], spp));
+  v = v > 0.0f ? v : 0.0f;
+  v = v < 0.999f ? v : 0.999f;
+  rgb8[i] = (uint8_t)(int)(256.0f * v);
+}
+
+extern "C" int rt_tonemap_device(const float *radiance_sum_dev, size_t n_values, int spp, uint8_t *rgb8_dev,
+                                 void *cuda_stream) {
+  if (!radiance_sum_dev || !rgb8_dev || spp <= 0)
+    return fail(RT_ERR_INVALID, "rt_tonemap_device: bad argument");
+  if (n_values == 0)
+    return RT_OK;
+  unsigned blocks = (unsigned)((n_values + 255) / 256);
+  tonemap_kernel<<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(radiance_sum_dev, n_values, (float)spp, rgb8_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RT_OK;
+}
+
+/* ------------------------------------------------------------------ render ------------------------------- */
+
+static int resolve_range(const rt_camera *cam, const rt_opts *opts, int *begin, int *count) {
+  if (cam->img_width <= 0 || cam->img_height <= 0 || cam->samples_per_pixel <= 0)
+    return fail(RT_ERR_INVALID, "render: empty image or no samples");
+  if ((long long)cam->img_width * cam->img_height > (1ll << 26))
+    return fail(RT_ERR_INVALID, "render: image larger than 2^26 pixels");
+  *begin = opts->sample_begin;
+  *count = opts->sample_count > 0 ? opts->sample_count : cam->samples_per_pixel - opts->sample_begin;
+  if (*begin < 0 || *count <= 0)
+    return fail(RT_ERR_INVALID, "render: empty sample range");
+  if (opts->rng_mode > RT_RNG_SAMPLE)
+    return fail(RT_ERR_INVALID, "render: unknown rng_mode");
+  if (opts->rng_mode == RT_RNG_PIXEL && *begin != 0)
+    return fail(RT_ERR_INVALID, "render: RT_RNG_PIXEL streams cannot start at sample %d", *begin);
+  return RT_OK;
+}
+
+/* enqueue one render into `radiance_dev` on `stream`; records ev[1]..ev[2] around the kernels */
+static int enqueue_render(rt_scene *s, const rt_camera *cam, const rt_opts *opts, float *radiance_dev,
+                          cudaStream_t stream) {
+  int begin = 0, count = 0;
+  int rc = resolve_range(cam, opts, &begin, &count);
+  if (rc != RT_OK)
+    return rc;
+  RenderJob job;
+  memset(&job, 0, sizeof(job));
+  job.cam = *cam;
+  job.sample_begin = begin, job.sample_count = count;
+  job.rng_mode = opts->rng_mode, job.flags = opts->flags;
+  job.radiance = radiance_dev;
+  job.counters = s->counters;
+  CUDA_TRY(cudaMemsetAsync(s->counters, 0, sizeof(RenderCounters), stream));
+
+  if (opts->kernel == RT_KERNEL_EXACT) {
+    if (cam->max_depth > 128)
+      return fail(RT_ERR_UNSUPPORTED, "render: the exact kernel unwinds at most 128 levels (max_depth %d)",
+                  cam->max_depth);
+    int n_threads = 0;
+    size_t need = exact_scratch_bytes(*cam, &n_threads);
+    rc = ensure(&s->scratch, &s->scratch_bytes, need);
+    if (rc != RT_OK)
+      return rc;
+    CUDA_TRY(cudaEventRecord(s->ev[1], stream));
+    CUDA_TRY(exact_render(s->view, job, s->scratch, n_threads, stream));
+    CUDA_TRY(cudaEventRecord(s->ev[2], stream));
+    s->last_launches = 1;
+  } else if (opts->kernel == RT_KERNEL_MEGA) {
+    if (!s->mega_ok)
+      return fail(RT_ERR_UNSUPPORTED, "render: %s (use RT_KERNEL_EXACT)", s->mega_why.c_str());
+    MegaPlan plan;
+    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, &plan));
+    rc = ensure(&s->scratch, &s->scratch_bytes, plan.partial_bytes);
+    if (rc != RT_OK)
+      return rc;
+    CUDA_TRY(cudaEventRecord(s->ev[1], stream));
+    CUDA_TRY(mega_render(s->view, job, plan, (float *)s->scratch, stream, &s->last_launches));
+    CUDA_TRY(cudaEventRecord(s->ev[2], stream));
+  } else {
+    return fail(RT_ERR_UNSUPPORTED, "render: kernel %u is not available in this build", opts->kernel);
+  }
+  return RT_OK;
+}
+
+static int collect_stats(rt_scene *s, rt_stats *stats, bool with_total) {
+  RenderCounters c;
+  CUDA_TRY(cudaMemcpy(&c, s->counters, sizeof(c), cudaMemcpyDeviceToHost));
+  rt_stats st;
+  memset(&st, 0, sizeof(st));
+  st.segments = c.segments, st.light_pdf_evals = c.light_pdf_evals, st.samples = c.samples;
+  st.nan_samples = c.nan_samples;
+  CUDA_TRY(cudaEventElapsedTime(&st.kernel_ms, s->ev[1], s->ev[2]));
+  if (with_total)
+    CUDA_TRY(cudaEventElapsedTime(&st.total_ms, s->ev[0], s->ev[3]));
+  st.launches = (uint32_t)s->last_launches;
+  s->last = st;
+  if (stats)
+    *stats = st;
+  return RT_OK;
+}
+
+extern "C" int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, float *radiance_sum_dev,
+                                void *cuda_stream) {
+  if (!scene || !camera || !opts || !radiance_sum_dev)
+    return fail(RT_ERR_INVALID, "rt_render_device: NULL argument");
+  DeviceGuard guard(scene->device);
+  return enqueue_render(scene, camera, opts, radiance_sum_dev, (cudaStream_t)cuda_stream);
+}
+
+extern "C" int rt_render_device_stats(rt_scene *scene, void *cuda_stream, rt_stats *stats) {
+  if (!scene)
+    return fail(RT_ERR_INVALID, "rt_render_device_stats: NULL scene");
+  DeviceGuard guard(scene->device);
+  CUDA_TRY(cudaStreamSynchronize((cudaStream_t)cuda_stream));
+  return collect_stats(scene, stats, false);
+}
+
+extern "C" int rt_render(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, float *radiance_sum,
+                         uint8_t *rgb8, rt_stats *stats) {
+  if (!scene || !camera || !opts)
+    return fail(RT_ERR_INVALID, "rt_render: NULL argument");
+  DeviceGuard guard(scene->device);
+  int begin = 0, count = 0;
+  int rc = resolve_range(camera, opts, &begin, &count);
+  if (rc != RT_OK)
+    return rc;
+  const size_t n_values = (size_t)camera->img_width * camera->img_height * 3;
+  rc = ensure((void **)&scene->radiance, &scene->radiance_bytes, n_values * sizeof(float));
+  if (rc == RT_OK)
+    rc = ensure((void **)&scene->rgb8, &scene->rgb8_bytes, n_values);
+  if (rc != RT_OK)
+    return rc;
+  cudaStream_t stream = nullptr;
+  CUDA_TRY(cudaEventRecord(scene->ev[0], stream));
+  rc = enqueue_render(scene, camera, opts, scene->radiance, stream);
+  if (rc != RT_OK)
+    return rc;
+  if (rgb8) {
+    rc = rt_tonemap_device(scene->radiance, n_values, count, scene->rgb8, stream);
+    if (rc != RT_OK)
+      return rc;
+    scene->last_launches++;
+    CUDA_TRY(cudaMemcpyAsync(rgb8, scene->rgb8, n_values, cudaMemcpyDeviceToHost, stream));
+  }
+  if (radiance_sum)
+    CUDA_TRY(cudaMemcpyAsync(radiance_sum, scene->radiance, n_values * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(cudaEventRecord(scene->ev[3], stream));
+  CUDA_TRY(cudaStreamSynchronize(stream));
+  return collect_stats(scene, stats, true);
+}
+
+/* ------------------------------------------------------------------ hit batch ---------------------------- */
+
+extern "C" int rt_hit_batch(rt_scene *scene, uint32_t kernel, size_t n, const float *origins, const float *dirs,
+                            float t_min, float t_max, uint64_t *rng_io, float *out_t, uint32_t *out_node, float *out_p,
+                            float *out_normal, float *out_uv, uint8_t *out_front, uint32_t *out_material) {
+  if (!scene || (n && (!origins || !dirs || !out_t || !out_node)))
+    return fail(RT_ERR_INVALID, "rt_hit_batch: NULL argument");
+  if (kernel != RT_KERNEL_EXACT && kernel != RT_KERNEL_MEGA && kernel != RT_KERNEL_WAVE)
+    return fail(RT_ERR_INVALID, "rt_hit_batch: unknown kernel");
+  if (kernel != RT_KERNEL_EXACT && !scene->mega_ok)
+    return fail(RT_ERR_UNSUPPORTED, "rt_hit_batch: %s (use RT_KERNEL_EXACT)", scene->mega_why.c_str());
+  if (n == 0)
+    return RT_OK;
+  DeviceGuard guard(scene->device);
+
+  struct Buf {
+    void *dev;
+    void *host;
+    size_t bytes;
+    bool in, out;
+  };
+  std::vector<Buf> bufs;
+  auto add = [&](const void *host, size_t bytes, bool in, bool out) -> void * {
+    if (!host)
+      return nullptr;
+    Buf b = {nullptr, const_cast<void *>(host), bytes, in, out};
+    if (cudaMalloc(&b.dev, bytes) != cudaSuccess)
+      return nullptr;
+    bufs.push_back(b);
+    return b.dev;
+  };
+  HitBatch hb;
+  memset(&hb, 0, sizeof(hb));
+  hb.n = n, hb.t_min = t_min, hb.t_max = t_max;
+  hb.origins = (const float *)add(origins, n * 12, true, false);
+  hb.dirs = (const float *)add(dirs, n * 12, true, false);
+  hb.rng_io = (uint64_t *)add(rng_io, n * 16, true, true);
+  hb.out_t = (float *)add(out_t, n * 4, false, true);
+  hb.out_node = (uint32_t *)add(out_node, n * 4, false, true);
+  hb.out_p = (float *)add(out_p, n * 12, false, true);
+  hb.out_normal = (float *)add(out_normal, n * 12, false, true);
+  hb.out_uv = (float *)add(out_uv, n * 8, false, true);
+  hb.out_front = (uint8_t *)add(out_front, n, false, true);
+  hb.out_material = (uint32_t *)add(out_material, n * 4, false, true);
+
+  cudaError_t err = cudaSuccess;
+  size_t expected = 4 + (rng_io ? 1 : 0) + (out_p ? 1 : 0) + (out_normal ? 1 : 0) + (out_uv ? 1 : 0) +
+                    (out_front ? 1 : 0) + (out_material ? 1 : 0);
+  if (bufs.size() != expected)
+    err = cudaErrorMemoryAllocation;
+  for (size_t k = 0; k < bufs.size() && err == cudaSuccess; k++)
+    if (bufs[k].in)
+      err = cudaMemcpy(bufs[k].dev, bufs[k].host, bufs[k].bytes, cudaMemcpyHostToDevice);
+  if (err == cudaSuccess)
+    err = kernel == RT_KERNEL_EXACT ? exact_hit_batch(scene->view, hb, nullptr) : mega_hit_batch(scene->view, hb, nullptr);
+  if (err == cudaSuccess)
+    err = cudaDeviceSynchronize();
+  for (size_t k = 0; k < bufs.size() && err == cudaSuccess; k++)
+    if (bufs[k].out)
+      err = cudaMemcpy(bufs[k].host, bufs[k].dev, bufs[k].bytes, cudaMemcpyDeviceToHost);
+  for (Buf &b : bufs)
+    cudaFree(b.dev);
+  if (err != cudaSuccess)
+    return fail(err == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA, "rt_hit_batch: %s",
+                cudaGetErrorString(err));
+  return RT_OK;
+}
+
+/* ------------------------------------------------------------------ single-process multi-GPU ------------- */
+
+__global__ void add_into_kernel(float *__restrict__ acc, const float *__restrict__ other, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    acc[i] += other[i];
+}
+
+extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camera, const rt_opts *opts, int n_gpus,
+                               float *radiance_sum, uint8_t *rgb8, rt_stats *stats) {
+  if (!desc || !camera || !opts || n_gpus < 1)
+    return fail(RT_ERR_INVALID, "rt_render_multi: bad argument");
+  const int have = rt_device_count();
+  if (have <= 0)
+    return fail(RT_ERR_NO_DEVICE, "rt_render_multi: no CUDA device");
+  if (n_gpus > have)
+    return fail(RT_ERR_INVALID, "rt_render_multi: %d GPUs requested, %d present", n_gpus, have);
+  int begin = 0, count = 0;
+  rt_opts base = *opts;
+  base.rng_mode = n_gpus > 1 ? (uint32_t)RT_RNG_SAMPLE : opts->rng_mode;
+  int rc = resolve_range(camera, &base, &begin, &count);
+  if (rc != RT_OK)
+    return rc;
+  if (count < n_gpus)
+    return fail(RT_ERR_INVALID, "rt_render_multi: fewer samples than GPUs");
+
+  const size_t n_values = (size_t)camera->img_width * camera->img_height * 3;
+  std::vector<rt_scene *> scenes(n_gpus, nullptr);
+  std::vector<cudaStream_t> streams(n_gpus, nullptr);
+  std::vector<float *> staging(n_gpus, nullptr); /* on device 0, one per peer */
+  std::vector<cudaEvent_t> done(n_gpus, nullptr);
+  auto cleanup = [&]() {
+    for (int g = 0; g < n_gpus; g++) {
+      if (scenes[g]) {
+        cudaSetDevice(scenes[g]->device);
+        if (streams[g])
+          cudaStreamDestroy(streams[g]);
+        if (done[g])
+          cudaEventDestroy(done[g]);
+      }
+      rt_scene_destroy(scenes[g]);
+    }
+    cudaSetDevice(0);
+    for (float *p : staging)
+      if (p)
+        cudaFree(p);
+  };
+#define MULTI_TRY(expr)                                                                                              \
+  do {                                                                                                               \
+    cudaError_t err__ = (expr);                                                                                      \
+    if (err__ != cudaSuccess) {                                                                                      \
+      cleanup();                                                                                                     \
+      return fail(RT_ERR_CUDA, "rt_render_multi: %s: %s", #expr, cudaGetErrorString(err__));                         \
+    }                                                                                                                \
+  } while (0)
+
+  int previous = 0;
+  cudaGetDevice(&previous);
+  for (int g = 0; g < n_gpus && rc == RT_OK; g++) {
+    rc = rt_scene_create(desc, g, &scenes[g]);
+    if (rc != RT_OK)
+      break;
+    MULTI_TRY(cudaSetDevice(g));
+    MULTI_TRY(cudaStreamCreateWithFlags(&streams[g], cudaStreamNonBlocking));
+    MULTI_TRY(cudaEventCreateWithFlags(&done[g], cudaEventDisableTiming));
+    rc = ensure((void **)&scenes[g]->radiance, &scenes[g]->radiance_bytes, n_values * sizeof(float));
+  }
+  if (rc != RT_OK) {
+    cleanup();
+    cudaSetDevice(previous);
+    return rc;
+  }
+  MULTI_TRY(cudaSetDevice(0));
+  rc = ensure((void **)&scenes[0]->rgb8, &scenes[0]->rgb8_bytes, n_values);
+  for (int g = 1; g < n_gpus; g++)
+    MULTI_TRY(cudaMalloc(&staging[g], n_values * sizeof(float)));
+  MULTI_TRY(cudaEventRecord(scenes[0]->ev[0], streams[0]));
+
+  /* sample range of GPU g: [begin + g*count/n, begin + (g+1)*count/n) */
+  for (int g = 0; g < n_gpus; g++) {
+    MULTI_TRY(cudaSetDevice(g));
+    rt_opts mine = base;
+    mine.sample_begin = begin + (int)((long long)count * g / n_gpus);
+    mine.sample_count = begin + (int)((long long)count * (g + 1) / n_gpus) - mine.sample_begin;
+    rc = enqueue_render(scenes[g], camera, &mine, scenes[g]->radiance, streams[g]);
+    if (rc != RT_OK) {
+      cleanup();
+      cudaSetDevice(previous);
+      return rc;
+    }
+    MULTI_TRY(cudaEventRecord(done[g], streams[g]));
+  }
+  /* gather over peer copies (NVLink when peer access exists) and sum on device 0 in GPU order */
+  MULTI_TRY(cudaSetDevice(0));
+  const unsigned blocks = (unsigned)((n_values + 255) / 256);
+  for (int g = 1; g < n_gpus; g++) {
+    MULTI_TRY(cudaStreamWaitEvent(streams[0], done[g], 0));
+    MULTI_TRY(cudaMemcpyPeerAsync(staging[g], 0, scenes[g]->radiance, g, n_values * sizeof(float), streams[0]));
+    add_into_kernel<<<blocks, 256, 0, streams[0]>>>(scenes[0]->radiance, staging[g], n_values);
+    MULTI_TRY(cudaGetLastError());
+  }
+  if (rgb8) {
+    rc = rt_tonemap_device(scenes[0]->radiance, n_values, count, scenes[0]->rgb8, streams[0]);
+    if (rc != RT_OK) {
+      cleanup();
+      cudaSetDevice(previous);
+      return rc;
+    }
+    MULTI_TRY(cudaMemcpyAsync(rgb8, scenes[0]->rgb8, n_values, cudaMemcpyDeviceToHost, streams[0]));
+  }
+  if (radiance_sum)
+    MULTI_TRY(cudaMemcpyAsync(radiance_sum, scenes[0]->radiance, n_values * sizeof(float), cudaMemcpyDeviceToHost,
+                              streams[0]));
+  MULTI_TRY(cudaEventRecord(scenes[0]->ev[3], streams[0]));
+  for (int g = 0; g < n_gpus; g++) {
+    MULTI_TRY(cudaSetDevice(g));
+    MULTI_TRY(cudaStreamSynchronize(streams[g]));
+  }
+  rt_stats total;
+  memset(&total, 0, sizeof(total));
+  for (int g = 0; g < n_gpus && rc == RT_OK; g++) {
+    cudaSetDevice(g);
+    rt_stats st;
+    rc = collect_stats(scenes[g], &st, g == 0);
+    total.segments += st.segments, total.light_pdf_evals += st.light_pdf_evals, total.samples += st.samples;
+    total.nan_samples += st.nan_samples;
+    total.kernel_ms = st.kernel_ms > total.kernel_ms ? st.kernel_ms : total.kernel_ms;
+    total.launches += st.launches;
+    if (g == 0)
+      total.total_ms = st.total_ms;
+  }
+  total.launches += (uint32_t)(n_gpus - 1) + (rgb8 ? 1u : 0u);
+  if (stats && rc == RT_OK)
+    *stats = total;
+  cleanup();
+  cudaSetDevice(previous);
+  return rc;
+#undef MULTI_TRY
+}
+
+/* ------------------------------------------------------------------ FP32 roofline probe ------------------ */
+
+__global__ void fp32_peak_kernel(float *out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f;
+  float a4 = a0 + 4.0f, a5 = a0 + 5.0f, a6 = a0 + 6.0f, a7 = a0 + 7.0f;
+  const float m = 0.999f, c = 1e-3f;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      a0 = fmaf(a0, m, c), a1 = fmaf(a1, m, c), a2 = fmaf(a2, m, c), a3 = fmaf(a3, m, c);
+      a4 = fmaf(a4, m, c), a5 = fmaf(a5, m, c), a6 = fmaf(a6, m, c), a7 = fmaf(a7, m, c);
+    }
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
+extern "C" int rt_fp32_peak(int device, float *tflops) {
+  if (!tflops)
+    return fail(RT_ERR_INVALID, "rt_fp32_peak: NULL argument");
+  if (rt_device_count() <= 0)
+    return fail(RT_ERR_NO_DEVICE, "rt_fp32_peak: no CUDA device");
+  if (device < 0)
+    CUDA_TRY(cudaGetDevice(&device));
+  DeviceGuard guard(device);
+  int sms = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  const int blocks = sms * 8, threads = 256, iters = 4096;
+  float *out = nullptr;
+  CUDA_TRY(cudaMalloc(&out, (size_t)blocks * threads * sizeof(float)));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  fp32_peak_kernel<<<blocks, threads>>>(out, 64); /* warm-up */
+  float best = 0.0f;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(e0);
+    fp32_peak_kernel<<<blocks, threads>>>(out, iters);
+    cudaEventRecord(e1);
+    cudaError_t err = cudaEventSynchronize(e1);
+    if (err != cudaSuccess) {
+      cudaFree(out);
+      return fail(RT_ERR_CUDA, "rt_fp32_peak: %s", cudaGetErrorString(err));
+    }
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    double flop = 2.0 * 8 * 16 * (double)iters * blocks * threads;
+    float tf = (float)(flop / (ms * 1e-3) * 1e-12);
+    best = tf > best ? tf : best;
+  }
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  cudaFree(out);
+  *tflops = best;
+  return RT_OK;
+}

@@ -1,0 +1,570 @@
+/*
+ * rtc_bvh.cu -- validation of an rt_scene_desc and construction of the rebuilt acceleration structure
+ * (see rtc_bvh.h).  Host code only.
+ */
+#include "rtc_bvh.h"
+#include "rtc_graph.cuh" /* the graph-machine limits */
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <set>
+
+/* ------------------------------------------------------------------ validation --------------------------- */
+
+std::string rtc_validate_desc(const rt_scene_desc &d) {
+  if (d.abi_version != RT_ABI_VERSION)
+    return "abi_version mismatch";
+  if (d.n_nodes == 0 || d.nodes == nullptr)
+    return "scene without nodes";
+  if ((d.n_children && !d.children) || (d.n_spheres && !d.spheres) || (d.n_quads && !d.quads) ||
+      (d.n_materials && !d.materials) || (d.n_textures && !d.textures) || (d.n_perlins && !d.perlins) ||
+      (d.n_images && !d.images) || (d.n_texel_bytes && !d.texels))
+    return "NULL array with a non-zero count";
+  if (d.objects_root >= d.n_nodes)
+    return "objects_root out of range";
+  if (d.lights_root != RT_NONE && d.lights_root >= d.n_nodes)
+    return "lights_root out of range";
+  if (d.n_nodes > 0x1FFFFFFu || d.n_spheres > 0x1FFFFFFu || d.n_quads > 0x1FFFFFFu)
+    return "scene too large for 25-bit references";
+
+  for (uint32_t i = 0; i < d.n_textures; i++) {
+    const rt_texture &t = d.textures[i];
+    switch (t.kind) {
+    case RT_TEX_SOLID: break;
+    case RT_TEX_CHECKER:
+      if (t.a >= d.n_textures || t.b >= d.n_textures)
+        return "checker texture child out of range";
+      if (t.a <= i || t.b <= i) /* the flattener emits children after parents: also rules out cycles */
+        return "checker texture children must follow their parent";
+      break;
+    case RT_TEX_IMAGE: {
+      if (t.a >= d.n_images)
+        return "image index out of range";
+      const rt_image &im = d.images[t.a];
+      if (im.width <= 0 || im.height <= 0 || im.offset + (uint64_t)im.width * im.height * 3 > d.n_texel_bytes)
+        return "image texels out of range";
+      break;
+    }
+    case RT_TEX_PERLIN:
+      if (t.a >= d.n_perlins)
+        return "perlin index out of range";
+      if (t.b > 64)
+        return "perlin depth out of range";
+      for (int k = 0; k < 256; k++) {
+        const rt_perlin &p = d.perlins[t.a];
+        if ((uint32_t)(p.perm_x[k] ^ p.perm_y[k] ^ p.perm_z[k]) > 255u || (uint32_t)p.perm_x[k] > 255u ||
+            (uint32_t)p.perm_y[k] > 255u || (uint32_t)p.perm_z[k] > 255u)
+          return "perlin permutation entry out of range";
+      }
+      break;
+    default: return "unknown texture kind";
+    }
+  }
+  for (uint32_t i = 0; i < d.n_materials; i++) {
+    const rt_material &m = d.materials[i];
+    if (m.tag > RT_MAT_ISOTROPIC)
+      return "unknown material tag";
+    bool needs_tex = m.tag == RT_MAT_LAMBERTIAN || m.tag == RT_MAT_METAL || m.tag == RT_MAT_DIFFUSE_LIGHT ||
+                     m.tag == RT_MAT_ISOTROPIC;
+    if (needs_tex && m.texture >= d.n_textures)
+      return "material texture out of range";
+  }
+  for (uint32_t i = 0; i < d.n_spheres; i++)
+    if (d.spheres[i].material >= d.n_materials || d.spheres[i].node >= d.n_nodes)
+      return "sphere material/node out of range";
+  for (uint32_t i = 0; i < d.n_quads; i++)
+    if (d.quads[i].material >= d.n_materials || d.quads[i].node >= d.n_nodes)
+      return "quad material/node out of range";
+
+  for (uint32_t i = 0; i < d.n_nodes; i++) {
+    const rt_node &n = d.nodes[i];
+    switch (n.kind) {
+    case RT_NODE_LIST:
+      if ((uint64_t)n.a + n.b > d.n_children)
+        return "list children out of range";
+      for (uint32_t k = 0; k < n.b; k++)
+        if (d.children[n.a + k] >= d.n_nodes)
+          return "list item out of range";
+      break;
+    case RT_NODE_SPHERE:
+      if (n.a >= d.n_spheres)
+        return "sphere index out of range";
+      break;
+    case RT_NODE_QUAD:
+      if (n.a >= d.n_quads)
+        return "quad index out of range";
+      break;
+    case RT_NODE_BVH:
+      if (n.a >= d.n_nodes || n.b >= d.n_nodes)
+        return "bvh child out of range";
+      break;
+    case RT_NODE_TRANSLATE:
+    case RT_NODE_ROTATE_Y:
+      if (n.a >= d.n_nodes)
+        return "instance child out of range";
+      break;
+    case RT_NODE_MEDIUM:
+      if (n.a >= d.n_nodes || n.b >= d.n_materials)
+        return "medium boundary/material out of range";
+      break;
+    default: return "unknown node kind";
+    }
+  }
+
+  /* acyclic: iterative DFS with colours */
+  std::vector<uint8_t> colour(d.n_nodes, 0);
+  std::function<bool(uint32_t, int)> dfs = [&](uint32_t id, int depth) -> bool {
+    if (depth > 4096 || colour[id] == 1)
+      return false;
+    if (colour[id] == 2)
+      return true;
+    colour[id] = 1;
+    const rt_node &n = d.nodes[id];
+    bool ok = true;
+    switch (n.kind) {
+    case RT_NODE_LIST:
+      for (uint32_t k = 0; k < n.b && ok; k++)
+        ok = dfs(d.children[n.a + k], depth + 1);
+      break;
+    case RT_NODE_BVH: ok = dfs(n.a, depth + 1) && dfs(n.b, depth + 1); break;
+    case RT_NODE_TRANSLATE:
+    case RT_NODE_ROTATE_Y:
+    case RT_NODE_MEDIUM: ok = dfs(n.a, depth + 1); break;
+    default: break;
+    }
+    colour[id] = 2;
+    return ok;
+  };
+  if (!dfs(d.objects_root, 0))
+    return "cycle (or absurd depth) in the Hittable graph";
+  if (d.lights_root != RT_NONE && !dfs(d.lights_root, 0))
+    return "cycle in the lights graph";
+  return "";
+}
+
+/* ------------------------------------------------------------------ graph-machine limits ----------------- */
+
+struct Depths {
+  int frames, rays, recs;
+};
+
+static Depths graph_depths(const rt_scene_desc &d, uint32_t id, std::vector<Depths> &memo) {
+  if (memo[id].frames)
+    return memo[id];
+  const rt_node &n = d.nodes[id];
+  Depths r = {1, 0, 0};
+  auto absorb = [&](uint32_t child, int extra_ray, int extra_rec) {
+    Depths c = graph_depths(d, child, memo);
+    r.frames = std::max(r.frames, 1 + c.frames);
+    r.rays = std::max(r.rays, extra_ray + c.rays);
+    r.recs = std::max(r.recs, extra_rec + c.recs);
+  };
+  switch (n.kind) {
+  case RT_NODE_LIST:
+    for (uint32_t k = 0; k < n.b; k++)
+      absorb(d.children[n.a + k], 0, 0);
+    break;
+  case RT_NODE_BVH:
+    absorb(n.a, 0, 0);
+    absorb(n.b, 0, 0);
+    break;
+  case RT_NODE_TRANSLATE:
+  case RT_NODE_ROTATE_Y: absorb(n.a, 1, 0); break;
+  case RT_NODE_MEDIUM: absorb(n.a, 0, 1); break;
+  default: break;
+  }
+  memo[id] = r;
+  return r;
+}
+
+/* nesting of lists under the lights root; -1 if some reachable list has no item to sample (would never return) */
+static int light_nesting(const rt_scene_desc &d, uint32_t id) {
+  const rt_node &n = d.nodes[id];
+  if (n.kind != RT_NODE_LIST)
+    return 0;
+  int deepest = 0, usable = 0;
+  for (uint32_t k = 0; k < n.b; k++) {
+    const rt_node &c = d.nodes[d.children[n.a + k]];
+    if (!(c.flags & RT_NODE_HAS_PDF))
+      continue;
+    usable++;
+    int sub = light_nesting(d, d.children[n.a + k]);
+    if (sub < 0)
+      return -1;
+    deepest = std::max(deepest, sub);
+  }
+  if (usable == 0)
+    return -1;
+  return 1 + deepest;
+}
+
+/* ------------------------------------------------------------------ the rebuilt structure ---------------- */
+
+namespace {
+
+struct Box {
+  float lo[3], hi[3];
+  void reset() {
+    for (int a = 0; a < 3; a++)
+      lo[a] = FLT_MAX, hi[a] = -FLT_MAX;
+  }
+  void grow(const Box &b) {
+    for (int a = 0; a < 3; a++)
+      lo[a] = std::min(lo[a], b.lo[a]), hi[a] = std::max(hi[a], b.hi[a]);
+  }
+  float area() const {
+    float e[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]};
+    if (e[0] < 0 || e[1] < 0 || e[2] < 0)
+      return 0.0f;
+    return 2.0f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
+  }
+};
+
+struct Item {
+  uint32_t kind;  /* REF_SPHERES / REF_QUADS / REF_INSTANCE */
+  uint32_t index; /* desc sphere / desc quad / built instance */
+  Box box;
+};
+
+constexpr int kMaxLeaf = 4;
+constexpr float kCostNode = 1.0f, kCostSphere = 0.8f, kCostQuad = 1.4f, kCostInstance = 4.0f;
+
+struct Builder {
+  const rt_scene_desc &d;
+  BuiltScene &out;
+  Builder(const rt_scene_desc &desc, BuiltScene &o) : d(desc), out(o) {}
+
+  static Box node_box(const rt_node &n) {
+    Box b;
+    for (int a = 0; a < 3; a++)
+      b.lo[a] = n.bbox[2 * a], b.hi[a] = n.bbox[2 * a + 1];
+    return b;
+  }
+  static float item_cost(uint32_t kind) {
+    return kind == REF_SPHERES ? kCostSphere : kind == REF_QUADS ? kCostQuad : kCostInstance;
+  }
+
+  void unsupported(const std::string &why) {
+    if (out.mega_supported) {
+      out.mega_supported = false;
+      out.mega_why = why;
+    }
+  }
+
+  /* object -> enclosing frame, applied from the innermost op outwards, the way the reference bounds its
+   * instances (hittable.c:336-344 Translate, :369-389 RotateY); padded because it is re-derived in float */
+  Box chain_to_outer(Box b, const std::vector<ChainOp> &chain, size_t from) const {
+    for (size_t k = chain.size(); k-- > from;) {
+      const ChainOp &op = chain[k];
+      if (!op.is_rotate) {
+        b.lo[0] += op.f0, b.hi[0] += op.f0;
+        b.lo[1] += op.f1, b.hi[1] += op.f1;
+        b.lo[2] += op.f2, b.hi[2] += op.f2;
+      } else {
+        const float sn = op.f0, cs = op.f1;
+        Box r;
+        r.reset();
+        for (int c = 0; c < 8; c++) {
+          float x = (c & 1) ? b.hi[0] : b.lo[0], y = (c & 2) ? b.hi[1] : b.lo[1], z = (c & 4) ? b.hi[2] : b.lo[2];
+          Box p;
+          p.lo[0] = p.hi[0] = cs * x + sn * z;
+          p.lo[1] = p.hi[1] = y;
+          p.lo[2] = p.hi[2] = -sn * x + cs * z;
+          r.grow(p);
+        }
+        b = r;
+      }
+    }
+    for (int a = 0; a < 3; a++) {
+      float pad = 1e-4f + 1e-5f * std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
+      b.lo[a] -= pad, b.hi[a] += pad;
+    }
+    return b;
+  }
+
+  /* Collects the primitives under `id` into `items` (the group being assembled).  `chain` holds the transforms
+   * between the group's frame and the current node; a transform node closes over its subtree as ONE instance
+   * whose chain is the full list of ops (instances never nest at traversal time). */
+  void collect(uint32_t id, std::vector<Item> &group_items, std::vector<Item> *inst_items,
+               std::vector<ChainOp> &chain, std::set<uint32_t> &seen, bool in_boundary,
+               std::vector<std::pair<uint32_t, std::vector<ChainOp>>> &media) {
+    const rt_node &n = d.nodes[id];
+    std::vector<Item> &dst = inst_items ? *inst_items : group_items;
+    switch (n.kind) {
+    case RT_NODE_LIST:
+      for (uint32_t k = 0; k < n.b; k++)
+        collect(d.children[n.a + k], group_items, inst_items, chain, seen, in_boundary, media);
+      break;
+    case RT_NODE_BVH:
+      collect(n.a, group_items, inst_items, chain, seen, in_boundary, media);
+      if (n.b != n.a)
+        collect(n.b, group_items, inst_items, chain, seen, in_boundary, media);
+      break;
+    case RT_NODE_SPHERE:
+    case RT_NODE_QUAD: {
+      if (!seen.insert(id).second)
+        break; /* the same object twice in one frame (BVH n==1 stores it as both children) */
+      Item it;
+      it.kind = n.kind == RT_NODE_SPHERE ? REF_SPHERES : REF_QUADS;
+      it.index = n.a;
+      it.box = node_box(n);
+      dst.push_back(it);
+      break;
+    }
+    case RT_NODE_TRANSLATE:
+    case RT_NODE_ROTATE_Y: {
+      ChainOp op;
+      op.is_rotate = n.kind == RT_NODE_ROTATE_Y;
+      op.f0 = n.f[0], op.f1 = n.f[1], op.f2 = n.f[2];
+      chain.push_back(op);
+      std::vector<Item> mine;
+      std::set<uint32_t> seen_inside;
+      collect(n.a, group_items, &mine, chain, seen_inside, in_boundary, media);
+      if (!mine.empty()) {
+        Box local;
+        local.reset();
+        for (const Item &it : mine)
+          local.grow(it.box);
+        Instance inst;
+        inst.op_begin = (uint32_t)out.ops.size();
+        inst.op_count = (uint32_t)chain.size();
+        inst.pad = 0;
+        out.ops.insert(out.ops.end(), chain.begin(), chain.end());
+        int depth = 0;
+        inst.root = build(mine, 0, mine.size(), depth);
+        blas_depth = std::max(blas_depth, depth);
+        Item it;
+        it.kind = REF_INSTANCE;
+        it.index = (uint32_t)out.insts.size();
+        it.box = chain_to_outer(local, chain, 0);
+        out.insts.push_back(inst);
+        group_items.push_back(it);
+      }
+      chain.pop_back();
+      break;
+    }
+    case RT_NODE_MEDIUM:
+      if (in_boundary)
+        unsupported("a ConstantMedium inside the boundary of another ConstantMedium");
+      else
+        media.push_back(std::make_pair(id, chain));
+      break;
+    default: break;
+    }
+  }
+
+  int blas_depth = 0;
+
+  uint32_t make_leaf(const std::vector<Item> &items, size_t lo, size_t hi) {
+    const uint32_t kind = items[lo].kind;
+    const uint32_t count = (uint32_t)(hi - lo);
+    if (kind == REF_INSTANCE)
+      return MAKE_REF(REF_INSTANCE, 1, items[lo].index);
+    if (kind == REF_SPHERES) {
+      uint32_t first = (uint32_t)out.msph.size();
+      for (size_t k = lo; k < hi; k++) {
+        const rt_sphere &s = d.spheres[items[k].index];
+        MSphere ms = {s.center[0], s.center[1], s.center[2], s.radius};
+        MPrimMeta meta = {s.material, s.node};
+        out.msph.push_back(ms);
+        out.msph_meta.push_back(meta);
+      }
+      return MAKE_REF(REF_SPHERES, count, first);
+    }
+    uint32_t first = (uint32_t)out.mquads.size();
+    for (size_t k = lo; k < hi; k++) {
+      const rt_quad &q = d.quads[items[k].index];
+      MQuad mq;
+      float mat_bits, node_bits;
+      memcpy(&mat_bits, &q.material, 4);
+      memcpy(&node_bits, &q.node, 4);
+      mq.n_D = make_float4(q.normal[0], q.normal[1], q.normal[2], q.D);
+      mq.q_mat = make_float4(q.Q[0], q.Q[1], q.Q[2], mat_bits);
+      mq.w_nod = make_float4(q.w[0], q.w[1], q.w[2], node_bits);
+      mq.u_ar = make_float4(q.u[0], q.u[1], q.u[2], q.area);
+      mq.v_ = make_float4(q.v[0], q.v[1], q.v[2], 0.0f);
+      out.mquads.push_back(mq);
+    }
+    return MAKE_REF(REF_QUADS, count, first);
+  }
+
+  /* binned SAH over items[lo, hi); reorders `items` in place; returns the reference of the subtree */
+  uint32_t build(std::vector<Item> &items, size_t lo, size_t hi, int &depth) {
+    const size_t n = hi - lo;
+    if (n == 0)
+      return REF_EMPTY;
+    Box bounds, cbounds;
+    bounds.reset(), cbounds.reset();
+    bool same_kind = true;
+    float leaf_cost = 0.0f;
+    for (size_t k = lo; k < hi; k++) {
+      bounds.grow(items[k].box);
+      Box c;
+      for (int a = 0; a < 3; a++)
+        c.lo[a] = c.hi[a] = 0.5f * (items[k].box.lo[a] + items[k].box.hi[a]);
+      cbounds.grow(c);
+      same_kind = same_kind && items[k].kind == items[lo].kind;
+      leaf_cost += item_cost(items[k].kind);
+    }
+    const bool leaf_allowed = same_kind && (items[lo].kind == REF_INSTANCE ? n == 1 : n <= (size_t)kMaxLeaf);
+    if (n == 1)
+      return make_leaf(items, lo, hi);
+
+    /* best split over 3 axes x 15 planes */
+    constexpr int kBins = 16;
+    int best_axis = -1, best_plane = -1;
+    float best_cost = FLT_MAX;
+    const float parent_area = std::max(bounds.area(), 1e-30f);
+    for (int axis = 0; axis < 3; axis++) {
+      float extent = cbounds.hi[axis] - cbounds.lo[axis];
+      if (!(extent > 0.0f))
+        continue;
+      Box bin_box[kBins];
+      float bin_cost[kBins];
+      int bin_n[kBins];
+      for (int b = 0; b < kBins; b++)
+        bin_box[b].reset(), bin_cost[b] = 0.0f, bin_n[b] = 0;
+      const float scale = (float)kBins / extent;
+      for (size_t k = lo; k < hi; k++) {
+        float c = 0.5f * (items[k].box.lo[axis] + items[k].box.hi[axis]);
+        int b = std::min(kBins - 1, std::max(0, (int)((c - cbounds.lo[axis]) * scale)));
+        bin_box[b].grow(items[k].box);
+        bin_cost[b] += item_cost(items[k].kind);
+        bin_n[b]++;
+      }
+      float right_area[kBins], right_cost[kBins];
+      Box acc;
+      acc.reset();
+      float cost = 0.0f;
+      for (int b = kBins - 1; b > 0; b--) {
+        acc.grow(bin_box[b]);
+        cost += bin_cost[b];
+        right_area[b] = acc.area(), right_cost[b] = cost;
+      }
+      acc.reset();
+      cost = 0.0f;
+      int left_n = 0;
+      for (int b = 0; b < kBins - 1; b++) {
+        acc.grow(bin_box[b]);
+        cost += bin_cost[b];
+        left_n += bin_n[b];
+        if (left_n == 0 || left_n == (int)n)
+          continue;
+        float sah = kCostNode + (acc.area() * cost + right_area[b + 1] * right_cost[b + 1]) / parent_area;
+        if (sah < best_cost)
+          best_cost = sah, best_axis = axis, best_plane = b;
+      }
+    }
+
+    if (leaf_allowed && (best_axis < 0 || leaf_cost <= best_cost))
+      return make_leaf(items, lo, hi);
+
+    size_t mid;
+    if (best_axis >= 0) {
+      const float extent = cbounds.hi[best_axis] - cbounds.lo[best_axis];
+      const float scale = (float)kBins / extent;
+      const float base = cbounds.lo[best_axis];
+      auto first_right = std::partition(items.begin() + lo, items.begin() + hi, [&](const Item &it) {
+        float c = 0.5f * (it.box.lo[best_axis] + it.box.hi[best_axis]);
+        int b = std::min(kBins - 1, std::max(0, (int)((c - base) * scale)));
+        return b <= best_plane;
+      });
+      mid = (size_t)(first_right - items.begin());
+    } else {
+      mid = lo + n / 2; /* coincident centroids: split by count */
+    }
+    if (mid == lo || mid == hi)
+      mid = lo + n / 2;
+
+    const uint32_t self = (uint32_t)out.bnodes.size();
+    out.bnodes.push_back(BNode());
+    int d0 = 0, d1 = 0;
+    Box b0, b1;
+    b0.reset(), b1.reset();
+    for (size_t k = lo; k < mid; k++)
+      b0.grow(items[k].box);
+    for (size_t k = mid; k < hi; k++)
+      b1.grow(items[k].box);
+    uint32_t c0 = build(items, lo, mid, d0);
+    uint32_t c1 = build(items, mid, hi, d1);
+    BNode node;
+    node.xy0 = make_float4(b0.lo[0], b0.hi[0], b0.lo[1], b0.hi[1]);
+    node.xy1 = make_float4(b1.lo[0], b1.hi[0], b1.lo[1], b1.hi[1]);
+    node.zz = make_float4(b0.lo[2], b0.hi[2], b1.lo[2], b1.hi[2]);
+    node.child0 = c0, node.child1 = c1, node.pad0 = 0, node.pad1 = 0;
+    out.bnodes[self] = node;
+    depth = 1 + std::max(d0, d1);
+    return MAKE_REF(REF_INNER, 1, self);
+  }
+
+  /* one group = everything under `root_node` seen from that node's own frame */
+  uint32_t build_group(uint32_t root_node, bool in_boundary,
+                       std::vector<std::pair<uint32_t, std::vector<ChainOp>>> &media, int &depth) {
+    std::vector<Item> items;
+    std::vector<ChainOp> chain;
+    std::set<uint32_t> seen;
+    blas_depth = 0;
+    collect(root_node, items, nullptr, chain, seen, in_boundary, media);
+    int tlas_depth = 0;
+    uint32_t root = build(items, 0, items.size(), tlas_depth);
+    depth = tlas_depth + 1 + blas_depth; /* +1: the sentinel that marks "leave the instance" */
+    return root;
+  }
+};
+
+} // namespace
+
+void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
+  out = BuiltScene();
+  std::vector<Depths> memo(d.n_nodes, Depths{0, 0, 0});
+  Depths g = graph_depths(d, d.objects_root, memo);
+  out.graph_frames = g.frames, out.graph_rays = g.rays + 1, out.graph_recs = g.recs + 1;
+  out.light_nesting = d.lights_root == RT_NONE ? 0 : light_nesting(d, d.lights_root);
+
+  Builder b(d, out);
+  std::vector<std::pair<uint32_t, std::vector<ChainOp>>> media, nested;
+  int depth = 0;
+  out.world_root = b.build_group(d.objects_root, false, media, depth);
+  out.max_stack = depth;
+  for (auto &m : media) {
+    const rt_node &n = d.nodes[m.first];
+    MMedium mm;
+    memset(&mm, 0, sizeof(mm));
+    mm.op_begin = (uint32_t)out.ops.size();
+    mm.op_count = (uint32_t)m.second.size();
+    out.ops.insert(out.ops.end(), m.second.begin(), m.second.end());
+    Box nb = Builder::node_box(n);
+    Box wb = b.chain_to_outer(nb, m.second, 0);
+    for (int a = 0; a < 3; a++)
+      mm.bbox[2 * a] = wb.lo[a], mm.bbox[2 * a + 1] = wb.hi[a];
+    int bdepth = 0;
+    mm.root = b.build_group(n.a, true, nested, bdepth);
+    out.max_stack = std::max(out.max_stack, bdepth);
+    mm.material = n.b;
+    mm.node = m.first;
+    mm.neg_inv_density = n.f[0];
+    out.media.push_back(mm);
+  }
+  /* keep every array non-empty so device pointers are never NULL */
+  if (out.bnodes.empty())
+    out.bnodes.push_back(BNode());
+  if (out.msph.empty()) {
+    out.msph.push_back(MSphere{0, 0, 0, 0});
+    out.msph_meta.push_back(MPrimMeta{0, 0});
+  }
+  if (out.mquads.empty())
+    out.mquads.push_back(MQuad());
+  if (out.insts.empty())
+    out.insts.push_back(Instance{0, 0, REF_EMPTY, 0});
+  if (out.ops.empty())
+    out.ops.push_back(ChainOp{0, 0, 0, 0});
+  if (out.media.empty()) {
+    MMedium z;
+    memset(&z, 0, sizeof(z));
+    z.root = REF_EMPTY;
+    out.media.push_back(z);
+    out.media.pop_back(); /* n_media stays 0; the upload pads */
+  }
+}

@@ -1,0 +1,38 @@
+/*
+ * rtc_bvh.h -- host-side construction of the structure the throughput kernels traverse.
+ *
+ * The reference builds its BVH by sorting along a RANDOM axis and splitting at the median
+ * (/root/reference/src/hittable.c:284-323), tests ~43 boxes per segment on the Book-1 scene, never bounds its
+ * Translate/RotateY instances (hittable.c:325-334,354-367) and keeps top-level items in a linear list.  For the
+ * megakernel we keep the reference's PRIMITIVES and TRANSFORMS (so hit distances stay bit-identical) but rebuild
+ * everything around them: one binned-SAH binary BVH per frame of reference ("group"), instances as leaves with
+ * conservative world-space bounds, media evaluated after the surfaces.
+ */
+#ifndef RTC_BVH_H
+#define RTC_BVH_H
+
+#include "rtc_scene.cuh"
+#include <string>
+#include <vector>
+
+struct BuiltScene {
+  std::vector<BNode> bnodes;
+  std::vector<MSphere> msph;
+  std::vector<MPrimMeta> msph_meta;
+  std::vector<MQuad> mquads;
+  std::vector<Instance> insts;
+  std::vector<ChainOp> ops;
+  std::vector<MMedium> media;
+  uint32_t world_root = REF_EMPTY;
+  int max_stack = 0; /* deepest traversal stack the kernels may need (entries) */
+  /* limits of the reference-order graph machine (rtc_graph.cuh) */
+  int graph_frames = 0, graph_rays = 0, graph_recs = 0, light_nesting = 0;
+  bool mega_supported = true;
+  std::string mega_why; /* why the rebuilt structure cannot express this graph (RT_ERR_UNSUPPORTED for mega/wave) */
+};
+
+/* Returns an empty string on success, else the reason the description is malformed (RT_ERR_INVALID). */
+std::string rtc_validate_desc(const rt_scene_desc &d);
+void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out);
+
+#endif /* RTC_BVH_H */

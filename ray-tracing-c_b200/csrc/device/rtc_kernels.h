@@ -1,0 +1,54 @@
+/*
+ * rtc_kernels.h -- internal launch interface between the C-ABI layer (rtc_api.cu) and the kernel translation
+ * units.  Not installed; the public surface is include/rtc_b200.h.
+ */
+#ifndef RTC_KERNELS_H
+#define RTC_KERNELS_H
+
+#include "rtc_scene.cuh"
+
+/* device-side counters of one render (reduced per warp, then atomically) */
+struct RenderCounters {
+  unsigned long long segments, light_pdf_evals, samples, nan_samples;
+  unsigned int next_item; /* dynamic work fetch of the persistent kernels */
+  unsigned int pad;
+};
+
+struct RenderJob {
+  rt_camera cam;
+  int sample_begin, sample_count;
+  uint32_t rng_mode, flags;
+  float *radiance;          /* float[h][w][3], overwritten with the per-pixel SUM over the rendered samples */
+  RenderCounters *counters; /* zeroed by the caller */
+};
+
+struct HitBatch {
+  size_t n;
+  const float *origins, *dirs;
+  float t_min, t_max;
+  uint64_t *rng_io;
+  float *out_t;
+  uint32_t *out_node;
+  float *out_p, *out_normal, *out_uv;
+  uint8_t *out_front;
+  uint32_t *out_material;
+};
+
+/* rtc_exact.cu: reference-order graph, portable math, recursion unwound exactly (bit-identical to the oracle) */
+size_t exact_scratch_bytes(const rt_camera &cam, int *n_threads);
+cudaError_t exact_render(const DScene &sc, const RenderJob &job, void *scratch, int n_threads, cudaStream_t stream);
+cudaError_t exact_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t stream);
+
+/* rtc_mega.cu: persistent megakernel over the rebuilt BVH */
+struct MegaPlan {
+  int blocks, threads;   /* persistent grid */
+  int chunk;             /* samples per work item */
+  int n_chunks;          /* work items per pixel */
+  size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */
+};
+cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, MegaPlan *plan);
+cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
+                        cudaStream_t stream, int *launches);
+cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t stream);
+
+#endif /* RTC_KERNELS_H */

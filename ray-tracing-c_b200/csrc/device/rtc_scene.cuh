@@ -1,0 +1,142 @@
+/*
+ * rtc_scene.cuh -- the device view of one flattened scene, the hit record, and the two primitive tests.
+ *
+ * Primitive tests are written with the strict (never contracted) operations of rtc_math.cuh in the reference's
+ * operation order, so that hit distances carry the reference's bits in every kernel:
+ *   sphere  /root/reference/src/hittable.c:120-151      quad  /root/reference/src/hittable.c:186-214
+ */
+#ifndef RTC_SCENE_CUH
+#define RTC_SCENE_CUH
+
+#include "rtc_b200.h"
+#include "rtc_math.cuh"
+
+/* ---- rebuilt acceleration structure (rtc_bvh.cpp builds it, rtc_mega.cu / rtc_wave.cu walk it) ---- */
+
+/* child / root reference: kind in bits 30-31, (count-1) in bits 25-29, index in bits 0-24 */
+#define REF_INNER 0u
+#define REF_SPHERES 1u
+#define REF_QUADS 2u
+#define REF_INSTANCE 3u
+#define REF_EMPTY 0xFFFFFFFFu
+#define REF_KIND(r) ((r) >> 30)
+#define REF_COUNT(r) ((((r) >> 25) & 31u) + 1u)
+#define REF_INDEX(r) ((r)&0x1FFFFFFu)
+#define MAKE_REF(kind, count, index) (((uint32_t)(kind) << 30) | (((uint32_t)(count)-1u) << 25) | (uint32_t)(index))
+
+/* binary node holding BOTH children's boxes: four 16-byte loads per visit */
+struct __align__(16) BNode {
+  float4 xy0; /* child0: x.lo x.hi y.lo y.hi */
+  float4 xy1; /* child1: x.lo x.hi y.lo y.hi */
+  float4 zz;  /* child0 z.lo z.hi, child1 z.lo z.hi */
+  uint32_t child0, child1, pad0, pad1;
+};
+
+/* sphere as the traversal reads it: one 16-byte load; material/node ids live in a side array */
+struct __align__(16) MSphere {
+  float cx, cy, cz, r;
+};
+struct __align__(8) MPrimMeta {
+  uint32_t material, node;
+};
+/* quad for the traversal: five 16-byte rows (the same numbers as rt_quad) */
+struct __align__(16) MQuad {
+  float4 n_D;   /* normal.xyz, D */
+  float4 q_mat; /* Q.xyz, material (bits) */
+  float4 w_nod; /* w.xyz, node (bits) */
+  float4 u_ar;  /* u.xyz, area */
+  float4 v_;    /* v.xyz, - */
+};
+
+/* one step of an instance's transform chain, outermost first (Translate: f = offset; RotateY: f0 = sin, f1 = cos) */
+struct __align__(16) ChainOp {
+  float f0, f1, f2;
+  uint32_t is_rotate;
+};
+struct __align__(16) Instance {
+  uint32_t op_begin, op_count, root, pad;
+};
+struct __align__(16) MMedium {
+  float bbox[6];           /* world-space bound of the boundary (conservative) */
+  uint32_t root;           /* boundary group */
+  uint32_t material, node; /* phase function, node id */
+  float neg_inv_density;
+  uint32_t op_begin, op_count; /* transforms ABOVE the medium itself */
+};
+
+struct DScene {
+  /* the reference-order graph exactly as flattened (rt_scene_desc arrays on the device) */
+  const rt_node *nodes;
+  const uint32_t *children;
+  const rt_sphere *spheres;
+  const rt_quad *quads;
+  const rt_material *materials;
+  const rt_texture *textures;
+  const rt_perlin *perlins;
+  const rt_image *images;
+  const uint8_t *texels;
+  uint32_t objects_root, lights_root;
+  /* the rebuilt structure */
+  const BNode *bnodes;
+  const MSphere *msph;
+  const MPrimMeta *msph_meta;
+  const MQuad *mquads;
+  const Instance *insts;
+  const ChainOp *ops;
+  const MMedium *media;
+  uint32_t world_root, n_media;
+};
+
+/* material.h:10-18 plus the id of the node that produced the hit */
+struct Hit {
+  V3 p, n;
+  uint32_t material;
+  float t, u, v;
+  int front;
+  uint32_t node;
+};
+
+/* ------------------------------------------------------------------ hittable.c:120-138 ------------------- */
+/* Distance only.  Returns true and writes *t when a root lies in the OPEN interval (t_min, t_max). */
+RTC_DEV bool sphere_isect(V3 center, float radius, V3 o, V3 d, float t_min, float t_max, float *t) {
+  V3 oc = sv_sub(o, center);
+  float a = sv_len2(d);
+  float b = sv_dot(oc, d);
+  float c = s_sub(sv_len2(oc), s_mul(radius, radius));
+  float disc = s_sub(s_mul(b, b), s_mul(a, c));
+  if (disc < 0.0f)
+    return false;
+  float sq = __fsqrt_rn(disc);
+  float root = s_div(s_sub(-b, sq), a);
+  if (root <= t_min || root >= t_max) {
+    root = s_div(s_add(-b, sq), a);
+    if (root <= t_min || root >= t_max)
+      return false;
+  }
+  *t = root;
+  return true;
+}
+
+/* ------------------------------------------------------------------ hittable.c:186-203 ------------------- */
+/* CLOSED interval [t_min, t_max]; alpha/beta are the quad's (u, v). */
+RTC_DEV bool quad_isect(V3 normal, float D, V3 Q, V3 w, V3 qu, V3 qv, V3 o, V3 d, float t_min, float t_max, float *t,
+                    float *alpha, float *beta) {
+  float denom = sv_dot(normal, d);
+  if (fabsf(denom) < 1e-8f)
+    return false;
+  float tt = s_div(s_sub(D, sv_dot(normal, o)), denom);
+  if (tt < t_min || tt > t_max)
+    return false;
+  V3 p = sv_at(o, d, tt);
+  V3 hp = sv_sub(p, Q);
+  float al = sv_dot(w, sv_cross(hp, qv));
+  float be = sv_dot(w, sv_cross(qu, hp));
+  if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
+    return false;
+  *t = tt;
+  *alpha = al;
+  *beta = be;
+  return true;
+}
+
+#endif /* RTC_SCENE_CUH */

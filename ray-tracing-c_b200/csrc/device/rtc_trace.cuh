@@ -1,0 +1,272 @@
+/*
+ * rtc_trace.cuh -- closest hit over the REBUILT structure (rtc_bvh.h): ordered traversal of a binary BVH whose
+ * nodes carry both children's boxes (four 16-byte loads per visit), primitives read with 16-byte loads,
+ * instances entered by transforming the ray with the reference's own operation sequence, media evaluated after
+ * the surfaces.  Replaces HittableList_hit / BVHNode_hit / AABB_hit / Translate_hit / RotateY_hit /
+ * ConstantMedium_hit (/root/reference/src/hittable.c:38-55, 74-88, 266-277, 325-423) on the throughput path.
+ *
+ * Hit distances come from sphere_isect / quad_isect (strict arithmetic), so they carry the reference's bits; what differs
+ * from the reference is only the ORDER in which candidates are met.  Ties are resolved as the reference's visiting
+ * order would (quads: the later node id wins, closed interval; spheres: open interval), see closer_quad().
+ */
+#ifndef RTC_TRACE_CUH
+#define RTC_TRACE_CUH
+
+#include "rtc_shade.cuh"
+
+#define TRACE_STACK 48          /* rt_scene_create refuses deeper structures for the mega/wave kernels */
+#define TRACE_SENTINEL 0xFFFFFFFEu
+#define PRIM_NONE 0xFFFFFFFFu
+#define PRIM_MEDIUM_KIND 3u     /* best_prim = MAKE_REF(3, 1, medium index) for a medium hit */
+
+struct Ray {
+  V3 o, d;
+};
+
+/* world (or enclosing-frame) ray -> object frame, op by op like Translate_hit / RotateY_hit (hittable.c:325-367) */
+RTC_DEV Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
+  for (uint32_t k = 0; k < op_count; k++) {
+    const float4 op = __ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k]));
+    if (__float_as_uint(op.w) == 0u) {
+      r.o = sv_sub(r.o, v3(op.x, op.y, op.z));
+    } else {
+      r.o = sv_rot_y(r.o, op.y, op.x);
+      r.d = sv_rot_y(r.d, op.y, op.x);
+    }
+  }
+  return r;
+}
+/* object frame -> world for a hit point and its normal, innermost op first */
+RTC_DEV void chain_unapply(const DScene &sc, uint32_t op_begin, uint32_t op_count, V3 &p, V3 &n) {
+  for (uint32_t k = op_count; k-- > 0;) {
+    const float4 op = __ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k]));
+    if (__float_as_uint(op.w) == 0u) {
+      p = sv_add(p, v3(op.x, op.y, op.z));
+    } else {
+      p = sv_rot_y_inv(p, op.y, op.x);
+      n = sv_rot_y_inv(n, op.y, op.x);
+    }
+  }
+}
+
+struct TraceHit {
+  float t;
+  uint32_t prim; /* PRIM_NONE, or kind/index reference into msph / mquads / media */
+  uint32_t inst; /* instance the primitive was met in, RT_NONE for the group's own frame */
+};
+
+struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * inv (one FMA per plane) */
+  V3 inv, oi;
+};
+RTC_DEV SlabRay slab_setup(const Ray &r) {
+  SlabRay s;
+  s.inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+  s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
+  return s;
+}
+
+/* Entry distance of the ray into the box, or +inf if it misses [t_min, t_max].  NaNs (0 * inf on an axis the ray
+ * is parallel to) are dropped by fminf/fmaxf, which errs on the side of visiting. */
+RTC_DEV float slab_entry(const SlabRay &s, float xlo, float xhi, float ylo, float yhi, float zlo, float zhi,
+                         float t_min, float t_max) {
+  float x0 = fmaf(xlo, s.inv.x, -s.oi.x), x1 = fmaf(xhi, s.inv.x, -s.oi.x);
+  float y0 = fmaf(ylo, s.inv.y, -s.oi.y), y1 = fmaf(yhi, s.inv.y, -s.oi.y);
+  float z0 = fmaf(zlo, s.inv.z, -s.oi.z), z1 = fmaf(zhi, s.inv.z, -s.oi.z);
+  float enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
+  float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+  leave = fmaf(fabsf(leave), 4e-7f, leave); /* two ulps of slack: never cull a hit the reference would find */
+  return enter <= leave ? enter : RTC_INF;
+}
+
+/* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame). */
+RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, float t_min, float t_max) {
+  TraceHit best;
+  best.t = t_max, best.prim = PRIM_NONE, best.inst = RT_NONE;
+  if (root == REF_EMPTY)
+    return best;
+
+  uint32_t stack[TRACE_STACK];
+  int sp = 0;
+  Ray r = r_in;
+  SlabRay slab = slab_setup(r);
+  uint32_t cur = root, cur_inst = RT_NONE;
+  uint32_t best_node = 0; /* node id of the best quad (only consulted on exact ties) */
+
+  for (;;) {
+    if (REF_KIND(cur) == REF_INNER) {
+      const BNode *n = &sc.bnodes[REF_INDEX(cur)];
+      const float4 xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
+      const uint4 ch = __ldg(reinterpret_cast<const uint4 *>(&n->child0));
+      float e0 = slab_entry(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t);
+      float e1 = slab_entry(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t);
+      bool h0 = e0 < RTC_INF, h1 = e1 < RTC_INF;
+      if (h0 && h1) {
+        bool swap = e1 < e0;
+        stack[sp++] = swap ? ch.x : ch.y;
+        cur = swap ? ch.y : ch.x;
+        continue;
+      }
+      if (h0 || h1) {
+        cur = h0 ? ch.x : ch.y;
+        continue;
+      }
+    } else if (REF_KIND(cur) == REF_SPHERES) {
+      const uint32_t first = REF_INDEX(cur), count = REF_COUNT(cur);
+      for (uint32_t k = 0; k < count; k++) {
+        const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
+        float t;
+        if (sphere_isect(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
+          best.t = t;
+          best.prim = MAKE_REF(REF_SPHERES, 1, first + k);
+          best.inst = cur_inst;
+        }
+      }
+    } else if (REF_KIND(cur) == REF_QUADS) {
+      const uint32_t first = REF_INDEX(cur), count = REF_COUNT(cur);
+      for (uint32_t k = 0; k < count; k++) {
+        const MQuad *q = &sc.mquads[first + k];
+        const float4 n_D = __ldg(&q->n_D);
+        /* plane distance first: most candidates die here, before the other four rows are read */
+        V3 nrm = v3(n_D.x, n_D.y, n_D.z);
+        float denom = sv_dot(nrm, r.d);
+        if (fabsf(denom) < 1e-8f)
+          continue;
+        float tt = s_div(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
+        if (tt < t_min || tt > best.t)
+          continue;
+        const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
+        V3 hp = sv_sub(sv_at(r.o, r.d, tt), v3(q_mat.x, q_mat.y, q_mat.z));
+        V3 w = v3(w_nod.x, w_nod.y, w_nod.z);
+        float al = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
+        float be = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
+        if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
+          continue;
+        const uint32_t node = __float_as_uint(w_nod.w);
+        /* exact tie with an earlier candidate: the reference keeps the LATER-visited quad (closed interval,
+         * hittable.c:194) and a quad always displaces a sphere at equal t; node ids are its visiting order */
+        if (tt == best.t && best.prim != PRIM_NONE && REF_KIND(best.prim) == REF_QUADS && node < best_node)
+          continue;
+        best.t = tt;
+        best.prim = MAKE_REF(REF_QUADS, 1, first + k);
+        best.inst = cur_inst;
+        best_node = node;
+      }
+    } else { /* instance: enter its frame; a sentinel on the stack brings the outer ray back */
+      const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
+      if (inst.z != REF_EMPTY) {
+        stack[sp++] = TRACE_SENTINEL;
+        cur_inst = REF_INDEX(cur);
+        r = chain_apply(sc, inst.x, inst.y, r_in);
+        slab = slab_setup(r);
+        cur = inst.z;
+        continue;
+      }
+    }
+    /* pop */
+    for (;;) {
+      if (sp == 0)
+        return best;
+      cur = stack[--sp];
+      if (cur != TRACE_SENTINEL)
+        break;
+      r = r_in;
+      slab = slab_setup(r);
+      cur_inst = RT_NONE;
+    }
+  }
+}
+
+static __device__ __noinline__ TraceHit trace_group_call(const DScene &sc, uint32_t root, const Ray &r, float t_min,
+                                                   float t_max) {
+  return trace_group(sc, root, r, t_min, t_max);
+}
+
+/* ConstantMedium_hit (hittable.c:392-423) for every medium of the scene, after the surfaces: two boundary
+ * queries, one draw when the clipped interval is not empty. */
+template <bool EXACT>
+__device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, float t_min, TraceHit &best, Rng &g) {
+  for (uint32_t m = 0; m < sc.n_media; m++) {
+    const MMedium *med = &sc.media[m];
+    Ray r = chain_apply(sc, med->op_begin, med->op_count, world);
+    TraceHit in = trace_group_call(sc, med->root, r, -RTC_INF, RTC_INF);
+    if (in.prim == PRIM_NONE)
+      continue;
+    TraceHit out = trace_group_call(sc, med->root, r, s_add(in.t, 0.0001f), RTC_INF);
+    if (out.prim == PRIM_NONE)
+      continue;
+    float in_t = fmaxf(in.t, t_min), out_t = fminf(out.t, best.t);
+    if (in_t >= out_t)
+      continue;
+    in_t = in_t > 0.0f ? in_t : 0.0f;
+    float ray_len = __fsqrt_rn(sv_len2(r.d));
+    float inside = s_mul(s_sub(out_t, in_t), ray_len);
+    float travel = s_mul(med->neg_inv_density, m_log<EXACT>(rng_f32(g)));
+    if (travel > inside)
+      continue;
+    best.t = s_add(in_t, s_div(travel, ray_len));
+    best.prim = MAKE_REF(PRIM_MEDIUM_KIND, 1, m);
+    best.inst = RT_NONE;
+  }
+}
+
+/* Full hit record (world frame) of a TraceHit.  WANT_UV = false skips the sphere's atan2f/acosf. */
+template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &world, const TraceHit &h, Hit &rec) {
+  rec.t = h.t;
+  const uint32_t kind = REF_KIND(h.prim), idx = REF_INDEX(h.prim);
+  if (kind == PRIM_MEDIUM_KIND) { /* only t, p, material (hittable.c:418-422) */
+    const MMedium *med = &sc.media[idx];
+    Ray r = chain_apply(sc, med->op_begin, med->op_count, world);
+    rec.p = sv_at(r.o, r.d, h.t);
+    rec.n = v3(0, 0, 0);
+    chain_unapply(sc, med->op_begin, med->op_count, rec.p, rec.n);
+    rec.material = med->material;
+    rec.node = med->node;
+    rec.u = rec.v = 0.0f;
+    rec.front = 0;
+    return;
+  }
+  Ray r = world;
+  uint32_t op_begin = 0, op_count = 0;
+  if (h.inst != RT_NONE) {
+    const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[h.inst]));
+    op_begin = inst.x, op_count = inst.y;
+    r = chain_apply(sc, op_begin, op_count, world);
+  }
+  if (kind == REF_SPHERES) {
+    const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[idx]));
+    const uint2 meta = __ldg(reinterpret_cast<const uint2 *>(&sc.msph_meta[idx]));
+    rec.material = meta.x;
+    rec.node = meta.y;
+    rec.u = rec.v = 0.0f;
+    const uint32_t tex = __ldg(&sc.materials[meta.x].texture);
+    if (EXACT || texture_needs_uv(sc, tex))
+      sphere_record<EXACT, true>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
+    else
+      sphere_record<EXACT, false>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
+  } else {
+    const MQuad *q = &sc.mquads[idx];
+    const float4 n_D = __ldg(&q->n_D), q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar),
+                 v_ = __ldg(&q->v_);
+    V3 nrm = v3(n_D.x, n_D.y, n_D.z), w = v3(w_nod.x, w_nod.y, w_nod.z);
+    rec.p = sv_at(r.o, r.d, h.t);
+    V3 hp = sv_sub(rec.p, v3(q_mat.x, q_mat.y, q_mat.z));
+    rec.u = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
+    rec.v = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
+    rec.material = __float_as_uint(q_mat.w);
+    rec.node = __float_as_uint(w_nod.w);
+    rec.front = sv_dot(r.d, nrm) < 0.0f;
+    rec.n = rec.front ? nrm : v_neg(nrm);
+  }
+  if (op_count)
+    chain_unapply(sc, op_begin, op_count, rec.p, rec.n);
+}
+
+/* The integrator's query (raytracing.c:45): surfaces, then media. */
+template <bool EXACT> RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
+  TraceHit best = trace_group(sc, sc.world_root, world, t_min, t_max);
+  if (sc.n_media)
+    trace_media<EXACT>(sc, world, t_min, best, g);
+  return best;
+}
+
+#endif /* RTC_TRACE_CUH */
