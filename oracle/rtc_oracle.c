@@ -90,7 +90,9 @@ typedef struct Ctx {
   const rt_scene_desc *d;
   int math;
   uint64_t segments, light_pdf_evals;
+  uint64_t work[5]; /* visits of the reference's own traversal: AABB, sphere, quad tests, medium evals, transforms */
 } Ctx;
+enum { W_AABB = 0, W_SPHERE = 1, W_QUAD = 2, W_MEDIUM = 3, W_XFORM = 4 };
 
 static inline float m_sin(const Ctx *c, float x) { return c->math == ORACLE_MATH_LIBM ? sinf(x) : pm_sinf(x); }
 static inline float m_cos(const Ctx *c, float x) { return c->math == ORACLE_MATH_LIBM ? cosf(x) : pm_cosf(x); }
@@ -118,7 +120,8 @@ static inline V3 ray_at(const Ray *r, float t) { return v3_add(r->o, v3_scale(r-
 
 /* ------------------------------------------------------------------ hittable.c:38-55 --------------------- */
 
-static bool aabb_hit(const float bbox[6], const Ray *r, float t_min, float t_max) {
+static bool aabb_hit(Ctx *c, const float bbox[6], const Ray *r, float t_min, float t_max) {
+  c->work[W_AABB]++;
   const float o[3] = {r->o.x, r->o.y, r->o.z}, d[3] = {r->d.x, r->d.y, r->d.z};
   for (int a = 0; a < 3; a++) {
     float inv = 1.0f / d[a];
@@ -139,7 +142,8 @@ static bool aabb_hit(const float bbox[6], const Ray *r, float t_min, float t_max
 
 /* ------------------------------------------------------------------ hittable.c:120-151 ------------------- */
 
-static bool sphere_hit(const Ctx *c, const rt_sphere *s, const Ray *r, float t_min, float t_max, Hit *rec) {
+static bool sphere_hit(Ctx *c, const rt_sphere *s, const Ray *r, float t_min, float t_max, Hit *rec) {
+  c->work[W_SPHERE]++;
   V3 center = v3_load(s->center);
   V3 oc = v3_sub(r->o, center);
   float a = v3_len2(r->d);
@@ -169,7 +173,8 @@ static bool sphere_hit(const Ctx *c, const rt_sphere *s, const Ray *r, float t_m
 
 /* ------------------------------------------------------------------ hittable.c:186-214 ------------------- */
 
-static bool quad_hit(const rt_quad *q, const Ray *r, float t_min, float t_max, Hit *rec) {
+static bool quad_hit(Ctx *c, const rt_quad *q, const Ray *r, float t_min, float t_max, Hit *rec) {
+  c->work[W_QUAD]++;
   V3 n = v3_load(q->normal);
   float denom = v3_dot(n, r->d);
   if (fabsf(denom) < 1e-8f)
@@ -212,7 +217,7 @@ static bool list_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, float 
 
 /* hittable.c:266-277: own box, then left ALWAYS before right, right sees the shrunk t_max */
 static bool bvh_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, float t_max, Hit *rec, Rng *g) {
-  if (!aabb_hit(n->bbox, r, t_min, t_max))
+  if (!aabb_hit(c, n->bbox, r, t_min, t_max))
     return false;
   bool left = node_hit(c, n->a, r, t_min, t_max, rec, g);
   if (left)
@@ -223,6 +228,7 @@ static bool bvh_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, float t
 
 /* hittable.c:325-334: no box test of its own; only p is moved back */
 static bool translate_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, float t_max, Hit *rec, Rng *g) {
+  c->work[W_XFORM]++;
   V3 offset = v3_load(n->f);
   Ray local = {v3_sub(r->o, offset), r->d};
   if (!node_hit(c, n->a, &local, t_min, t_max, rec, g))
@@ -235,6 +241,7 @@ static bool translate_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, f
 static inline V3 rot_y(V3 u, float cs, float sn) { return v3(cs * u.x - sn * u.z, u.y, sn * u.x + cs * u.z); }
 static inline V3 rot_y_inv(V3 u, float cs, float sn) { return v3(cs * u.x + sn * u.z, u.y, -sn * u.x + cs * u.z); }
 static bool rotate_y_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, float t_max, Hit *rec, Rng *g) {
+  c->work[W_XFORM]++;
   float sn = n->f[0], cs = n->f[1];
   Ray local = {rot_y(r->o, cs, sn), rot_y(r->d, cs, sn)};
   if (!node_hit(c, n->a, &local, t_min, t_max, rec, g))
@@ -248,6 +255,7 @@ static bool rotate_y_hit(Ctx *c, const rt_node *n, const Ray *r, float t_min, fl
  * normal / front / u / v of `rec` are left as earlier candidates wrote them */
 static bool medium_hit(Ctx *c, uint32_t id, const rt_node *n, const Ray *r, float t_min, float t_max, Hit *rec,
                        Rng *g) {
+  c->work[W_MEDIUM]++;
   Hit in, out;
   memset(&in, 0, sizeof(in));
   memset(&out, 0, sizeof(out));
@@ -277,7 +285,7 @@ static bool node_hit(Ctx *c, uint32_t id, const Ray *r, float t_min, float t_max
   switch (n->kind) {
   case RT_NODE_LIST: return list_hit(c, n, r, t_min, t_max, rec, g);
   case RT_NODE_SPHERE: return sphere_hit(c, &c->d->spheres[n->a], r, t_min, t_max, rec);
-  case RT_NODE_QUAD: return quad_hit(&c->d->quads[n->a], r, t_min, t_max, rec);
+  case RT_NODE_QUAD: return quad_hit(c, &c->d->quads[n->a], r, t_min, t_max, rec);
   case RT_NODE_BVH: return bvh_hit(c, n, r, t_min, t_max, rec, g);
   case RT_NODE_TRANSLATE: return translate_hit(c, n, r, t_min, t_max, rec, g);
   case RT_NODE_ROTATE_Y: return rotate_y_hit(c, n, r, t_min, t_max, rec, g);
@@ -328,9 +336,9 @@ static V3 sphere_rand(Ctx *c, const rt_sphere *s, V3 origin, Rng *g) {
   Basis b = basis_from_w(oc);
   return basis_local(&b, v3(x, y, z));
 }
-static float quad_pdf(const rt_quad *q, const Ray *r) {
+static float quad_pdf(Ctx *c, const rt_quad *q, const Ray *r) {
   Hit rec;
-  if (!quad_hit(q, r, 0.001f, INFINITY, &rec))
+  if (!quad_hit(c, q, r, 0.001f, INFINITY, &rec))
     return 0.0f;
   float d2 = rec.t * rec.t * v3_len2(r->d);
   float cos_theta = fabsf(v3_dot(rec.n, v3_unit(r->d)));
@@ -346,7 +354,7 @@ static float node_pdf(Ctx *c, uint32_t id, const Ray *r, Rng *g) {
   const rt_node *n = &c->d->nodes[id];
   switch (n->kind) {
   case RT_NODE_SPHERE: return sphere_pdf(c, &c->d->spheres[n->a], r);
-  case RT_NODE_QUAD: return quad_pdf(&c->d->quads[n->a], r);
+  case RT_NODE_QUAD: return quad_pdf(c, &c->d->quads[n->a], r);
   case RT_NODE_LIST: {
     float sum = 0.0f, count = 0.0f;
     for (uint32_t i = 0; i < n->b; i++) {
@@ -561,6 +569,12 @@ static inline uint8_t tonemap(float sum, int spp) { /* raytracing.c:127-131 with
   return (uint8_t)(int)(256.0f * v);
 }
 
+/* Visits of the last oracle_render: {AABB tests, sphere tests, quad tests, medium evaluations, instance transforms,
+ * segments}.  Light-pdf self-hits are included in the sphere/quad counts, as in SURVEY.md's probe.  Basis of the
+ * algorithmic-FLOP figure bench.py quotes the roofline fraction against. */
+static uint64_t g_last_work[6];
+void oracle_last_work(uint64_t out[6]) { memcpy(out, g_last_work, sizeof(g_last_work)); }
+
 /* Exported.  radiance_sum: float[h][w][3] (may be NULL), rgb8: uint8[h][w][3] (may be NULL).
  * opts->kernel is ignored; opts->reserved[0] carries the math mode (ORACLE_MATH_*). */
 int oracle_render(const rt_scene_desc *desc, const rt_camera *cam, const rt_opts *opts, int math, float *radiance_sum,
@@ -572,12 +586,13 @@ int oracle_render(const rt_scene_desc *desc, const rt_camera *cam, const rt_opts
     return RT_ERR_INVALID; /* one stream per pixel cannot start in the middle */
 
   uint64_t segments = 0, pdf_evals = 0, nan_samples = 0;
+  uint64_t w_aabb = 0, w_sphere = 0, w_quad = 0, w_medium = 0, w_xform = 0;
   const V3 px00 = v3_load(cam->pixel00), du = v3_load(cam->pixel_delta_u), dv = v3_load(cam->pixel_delta_v);
   const V3 eye = v3_load(cam->origin), lens_u = v3_load(cam->dof_disc_u), lens_v = v3_load(cam->dof_disc_v);
 
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : segments, pdf_evals, nan_samples)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : segments, pdf_evals, nan_samples, w_aabb, w_sphere, w_quad, w_medium, w_xform)
   for (int j = 0; j < h; j++) {
-    Ctx ctx = {desc, math, 0, 0};
+    Ctx ctx = {desc, math, 0, 0, {0, 0, 0, 0, 0}};
     for (int i = 0; i < w; i++) {
       Rng rng;
       rng_seed(&rng, 17 + (uint64_t)j, 23 + (uint64_t)i);
@@ -624,7 +639,11 @@ int oracle_render(const rt_scene_desc *desc, const rt_camera *cam, const rt_opts
     }
     segments += ctx.segments;
     pdf_evals += ctx.light_pdf_evals;
+    w_aabb += ctx.work[W_AABB], w_sphere += ctx.work[W_SPHERE], w_quad += ctx.work[W_QUAD];
+    w_medium += ctx.work[W_MEDIUM], w_xform += ctx.work[W_XFORM];
   }
+  g_last_work[0] = w_aabb, g_last_work[1] = w_sphere, g_last_work[2] = w_quad, g_last_work[3] = w_medium;
+  g_last_work[4] = w_xform, g_last_work[5] = segments;
   if (stats) {
     memset(stats, 0, sizeof(*stats));
     stats->segments = segments;
@@ -647,7 +666,7 @@ int oracle_hit_batch(const rt_scene_desc *desc, int math, size_t n, const float 
                      float *out_normal, float *out_uv, uint8_t *out_front, uint32_t *out_material) {
 #pragma omp parallel for schedule(static)
   for (size_t i = 0; i < n; i++) {
-    Ctx ctx = {desc, math, 0, 0};
+    Ctx ctx = {desc, math, 0, 0, {0, 0, 0, 0, 0}};
     Ray r = {v3_load(origins + 3 * i), v3_load(dirs + 3 * i)};
     Rng g = {0, 1};
     if (rng_io) {

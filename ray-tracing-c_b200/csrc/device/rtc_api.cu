@@ -217,11 +217,11 @@ extern "C" int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info) 
   BuiltScene b;
   rtc_build_scene(*desc, b);
   memset(info, 0, sizeof(*info));
-  info->bvh_nodes = (uint32_t)b.bnodes.size();
+  info->bvh_nodes = b.n_bnodes;
   info->bvh_depth = (uint32_t)b.max_stack;
-  info->spheres = (uint32_t)b.msph.size(), info->quads = (uint32_t)b.mquads.size();
-  info->instances = (uint32_t)b.insts.size(), info->media = (uint32_t)b.media.size();
-  info->chain_ops = (uint32_t)b.ops.size();
+  info->spheres = b.n_msph, info->quads = b.n_mquads;
+  info->instances = b.n_insts, info->media = (uint32_t)b.media.size();
+  info->chain_ops = b.n_ops;
   info->graph_frames = (uint32_t)b.graph_frames, info->graph_rays = (uint32_t)b.graph_rays;
   info->graph_recs = (uint32_t)b.graph_recs;
   info->light_nesting = b.light_nesting;

@@ -547,6 +547,9 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
     mm.neg_inv_density = n.f[0];
     out.media.push_back(mm);
   }
+  out.n_bnodes = (uint32_t)out.bnodes.size(), out.n_msph = (uint32_t)out.msph.size();
+  out.n_mquads = (uint32_t)out.mquads.size(), out.n_insts = (uint32_t)out.insts.size();
+  out.n_ops = (uint32_t)out.ops.size();
   /* keep every array non-empty so device pointers are never NULL */
   if (out.bnodes.empty())
     out.bnodes.push_back(BNode());

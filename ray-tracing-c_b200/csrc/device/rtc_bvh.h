@@ -24,6 +24,7 @@ struct BuiltScene {
   std::vector<ChainOp> ops;
   std::vector<MMedium> media;
   uint32_t world_root = REF_EMPTY;
+  uint32_t n_bnodes = 0, n_msph = 0, n_mquads = 0, n_insts = 0, n_ops = 0; /* before padding to non-empty */
   int max_stack = 0; /* deepest traversal stack the kernels may need (entries) */
   /* limits of the reference-order graph machine (rtc_graph.cuh) */
   int graph_frames = 0, graph_rays = 0, graph_recs = 0, light_nesting = 0;

@@ -60,7 +60,11 @@ struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * i
 };
 RTC_DEV SlabRay slab_setup(const Ray &r) {
   SlabRay s;
-  s.inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+  /* a direction component of exactly 0 would give inv = inf and plane*inf - o*inf = NaN for BOTH planes of the
+   * axis, losing the "origin outside the slab" rejection and, with mixed-sign bounds, even the sign; a huge finite
+   * reciprocal keeps every product ordered (scene coordinates are far below 3e8) */
+  s.inv = v3(copysignf(fminf(fabsf(1.0f / r.d.x), 1e30f), r.d.x), copysignf(fminf(fabsf(1.0f / r.d.y), 1e30f), r.d.y),
+             copysignf(fminf(fabsf(1.0f / r.d.z), 1e30f), r.d.z));
   s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
   return s;
 }

@@ -89,3 +89,21 @@ def pcg32(initstate, initseq, n):
     out = np.empty(n, np.uint32)
     oracle().oracle_pcg32(initstate, initseq, n, out.ctypes.data)
     return out
+
+
+# the algorithmic-work model of SURVEY.md section 8(d): FLOP per visit of the REFERENCE's own traversal
+FLOP_AABB, FLOP_SPHERE, FLOP_QUAD, FLOP_MEDIUM, FLOP_XFORM, FLOP_FINALISE, FLOP_SCATTER = 27, 24, 36, 30, 14, 40, 60
+
+
+def last_work() -> dict:
+    """Visits of the last render(): AABB / sphere / quad tests, medium evaluations, instance transforms, segments."""
+    out = (C.c_uint64 * 6)()
+    oracle().oracle_last_work(out)
+    keys = ("aabb", "sphere", "quad", "medium", "xform", "segments")
+    return dict(zip(keys, [int(v) for v in out]))
+
+
+def flop_per_segment(work: dict) -> float:
+    seg = max(work["segments"], 1)
+    return (FLOP_AABB * work["aabb"] + FLOP_SPHERE * work["sphere"] + FLOP_QUAD * work["quad"] +
+            FLOP_MEDIUM * work["medium"] + FLOP_XFORM * work["xform"]) / seg + FLOP_FINALISE + FLOP_SCATTER
