@@ -339,6 +339,7 @@ def b200_arm(args):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(info["device_bytes"]) + 128,
                 "d2h_bytes_per_step": n_values + 48, "ms_per_step": float(e2e_t.item()),
+                "ms_steps": [round(v, 2) for v in e2e_ms], "kernel_ms_last": st_e.get("kernel_ms"), "device_total_ms_last": st_e.get("total_ms"),
                 "api": "Camera_render (rtc_camera_render_opts): flatten + BVH build + upload + kernels + download"
                        if world == 1 else "rt_scene_create + rt_render_device + NCCL reduce + tonemap + D2H per rank"},
         "gpu_launches": launches,

@@ -52,8 +52,10 @@ __global__ void __launch_bounds__(MEGA_BLOCK)
   int pi = 0, pj = 0, s = 0, s_end = 0, depth = 0, chunk_id = 0;
   bool have_item = false, alive = false;
 
+  bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
   for (;;) {
-    if (!alive) {
+    /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
+    if (!alive && !done) {
       if (have_item && s == s_end) { /* chunk finished: one store per item */
         float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)w * h * 3 : job.radiance) +
                      ((size_t)pj * w + pi) * 3;
@@ -80,39 +82,50 @@ __global__ void __launch_bounds__(MEGA_BLOCK)
           break;
         }
         if (!have_item)
-          break; /* no work left for this lane */
+          done = true;
       }
-      /* camera ray of sample s (raytracing.c:100-122) */
-      if (job.rng_mode == RT_RNG_SAMPLE)
-        rng_seed_sample(rng, pi, pj, s);
-      float jx = rng_between(rng, -0.5f, 0.5f);
-      float jy = rng_between(rng, -0.5f, 0.5f);
-      ray.o = eye;
-      if (cam.dof_angle > 0.0f) {
-        float a, b;
-        for (;;) {
-          a = rng_between(rng, -1.0f, 1.0f);
-          b = rng_between(rng, -1.0f, 1.0f);
-          if (a * a + b * b < 1.0f)
-            break;
+      if (!done) { /* camera ray of sample s (raytracing.c:100-122) */
+        if (job.rng_mode == RT_RNG_SAMPLE)
+          rng_seed_sample(rng, pi, pj, s);
+        float jx = rng_between(rng, -0.5f, 0.5f);
+        float jy = rng_between(rng, -0.5f, 0.5f);
+        ray.o = eye;
+        if (cam.dof_angle > 0.0f) {
+          float a, b;
+          for (;;) {
+            a = rng_between(rng, -1.0f, 1.0f);
+            b = rng_between(rng, -1.0f, 1.0f);
+            if (a * a + b * b < 1.0f)
+              break;
+          }
+          ray.o = v_add(v_add(eye, v_scale(lens_u, a)), v_scale(lens_v, b));
         }
-        ray.o = v_add(v_add(eye, v_scale(lens_u, a)), v_scale(lens_v, b));
+        ray.d = v_add(v_add(v_add(pixel, v_scale(du, jx)), v_scale(dv, jy)), v_neg(ray.o));
+        beta = v3(1, 1, 1);
+        L = v3(0, 0, 0);
+        depth = 0;
+        alive = max_depth > 0;
+        n_samples++;
+        if (!alive)
+          s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
       }
-      ray.d = v_add(v_add(v_add(pixel, v_scale(du, jx)), v_scale(dv, jy)), v_neg(ray.o));
-      beta = v3(1, 1, 1);
-      L = v3(0, 0, 0);
-      depth = 0;
-      alive = true;
-      n_samples++;
     }
+    /* warp-uniform exit, and the point where all 32 lanes meet again before the traversal */
+    if (__all_sync(0xffffffffu, done))
+      break;
 
-    /* ---- one segment ---- */
-    bool ended = false;
-    if (depth >= max_depth) {
-      ended = true; /* raytracing.c:40-41: contributes nothing */
-    } else {
+    /* ---- phase 2: one closest-hit query for every live lane, entered together */
+    TraceHit th;
+    th.t = RTC_INF, th.prim = PRIM_NONE, th.inst = RT_NONE;
+    if (alive) {
       n_segments++;
-      TraceHit th = trace_world<false>(sc, ray, 1e-3f, RTC_INF, rng);
+      th = trace_world<false>(sc, ray, 1e-3f, RTC_INF, rng);
+    }
+    __syncwarp();
+
+    /* ---- phase 3: shade */
+    if (alive) {
+      bool ended = false;
       if (th.prim == PRIM_NONE) {
         L = v_add(L, v_mul(beta, background));
         ended = true;
@@ -141,21 +154,23 @@ __global__ void __launch_bounds__(MEGA_BLOCK)
           ray.o = rec.p;
           ray.d = r_out;
           depth++;
+          ended = depth >= max_depth; /* the next call would return 0 (raytracing.c:40-41) */
+        }
+      }
+      if (ended) {
+        alive = false;
+        s++;
+        if (has_nan3(L)) {
+          n_nan++;
+          if (!(job.flags & RT_FLAG_DROP_NAN))
+            sum = v_add(sum, L);
+        } else {
+          sum = v_add(sum, L);
         }
       }
     }
-    if (ended) {
-      alive = false;
-      s++;
-      if (has_nan3(L)) {
-        n_nan++;
-        if (!(job.flags & RT_FLAG_DROP_NAN))
-          sum = v_add(sum, L);
-      } else {
-        sum = v_add(sum, L);
-      }
-    }
   }
+  /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
 
   unsigned long long v[4] = {n_segments, n_pdf, n_samples, n_nan};
   __syncwarp();

@@ -60,11 +60,14 @@ struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * i
 };
 RTC_DEV SlabRay slab_setup(const Ray &r) {
   SlabRay s;
-  /* a direction component of exactly 0 would give inv = inf and plane*inf - o*inf = NaN for BOTH planes of the
-   * axis, losing the "origin outside the slab" rejection and, with mixed-sign bounds, even the sign; a huge finite
-   * reciprocal keeps every product ordered (scene coordinates are far below 3e8) */
-  s.inv = v3(copysignf(fminf(fabsf(1.0f / r.d.x), 1e30f), r.d.x), copysignf(fminf(fabsf(1.0f / r.d.y), 1e30f), r.d.y),
-             copysignf(fminf(fabsf(1.0f / r.d.z), 1e30f), r.d.z));
+  /* |1/d| is capped at 1e30 so that plane*inv and o*inv never overflow to inf - inf (scene coordinates are far
+   * below 3e8).  A component of EXACTLY zero gets NaN: both planes of that axis then drop out of fminf/fmaxf, i.e.
+   * the axis is ignored, which errs on the side of visiting.  (The reference's (plane - o) * inf also yields NaN
+   * when the ray lies in a face plane -- hittable.c:40-42 -- and a finite stand-in would turn that into a miss.) */
+  const float qnan = __int_as_float(0x7fc00000);
+  s.inv = v3(r.d.x == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.x), 1e30f), r.d.x),
+             r.d.y == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.y), 1e30f), r.d.y),
+             r.d.z == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.z), 1e30f), r.d.z));
   s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
   return s;
 }
@@ -82,6 +85,26 @@ RTC_DEV float slab_entry(const SlabRay &s, float xlo, float xhi, float ylo, floa
   return enter <= leave ? enter : RTC_INF;
 }
 
+/* sphere_isect with t_max INCLUDED, so that the traversal can see exact ties and resolve them like the reference */
+RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float t_min, float t_max, float *t) {
+  V3 oc = sv_sub(o, center);
+  float a = sv_len2(d);
+  float b = sv_dot(oc, d);
+  float c = s_sub(sv_len2(oc), s_mul(radius, radius));
+  float disc = s_sub(s_mul(b, b), s_mul(a, c));
+  if (disc < 0.0f)
+    return false;
+  float sq = __fsqrt_rn(disc);
+  float root = s_div(s_sub(-b, sq), a);
+  if (root <= t_min || root > t_max) {
+    root = s_div(s_add(-b, sq), a);
+    if (root <= t_min || root > t_max)
+      return false;
+  }
+  *t = root;
+  return true;
+}
+
 /* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame). */
 RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, float t_min, float t_max) {
   TraceHit best;
@@ -96,11 +119,27 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, f
   uint32_t cur = root, cur_inst = RT_NONE;
   uint32_t best_node = 0; /* node id of the best quad (only consulted on exact ties) */
 
+  /* pops the next subtree; leaving an instance (sentinel) restores the outer ray */
+  auto pop = [&]() -> uint32_t {
+    for (;;) {
+      if (sp == 0)
+        return REF_EMPTY;
+      uint32_t c = stack[--sp];
+      if (c != TRACE_SENTINEL)
+        return c;
+      r = r_in;
+      slab = slab_setup(r);
+      cur_inst = RT_NONE;
+    }
+  };
+
+  /* "while-while": all lanes of a warp first walk inner nodes together until each holds a leaf (or is done), then
+   * all process leaves together -- keeps the 32 lanes in the same code far more often than one if/else per step */
   for (;;) {
-    if (REF_KIND(cur) == REF_INNER) {
+    while (REF_KIND(cur) == REF_INNER) {
       const BNode *n = &sc.bnodes[REF_INDEX(cur)];
       const float4 xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
-      const uint4 ch = __ldg(reinterpret_cast<const uint4 *>(&n->child0));
+      const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(&n->child0));
       float e0 = slab_entry(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t);
       float e1 = slab_entry(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t);
       bool h0 = e0 < RTC_INF, h1 = e1 < RTC_INF;
@@ -108,18 +147,28 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, f
         bool swap = e1 < e0;
         stack[sp++] = swap ? ch.x : ch.y;
         cur = swap ? ch.y : ch.x;
-        continue;
-      }
-      if (h0 || h1) {
+      } else if (h0 || h1) {
         cur = h0 ? ch.x : ch.y;
-        continue;
+      } else {
+        cur = pop();
       }
-    } else if (REF_KIND(cur) == REF_SPHERES) {
+    }
+    if (cur == REF_EMPTY)
+      break;
+    if (REF_KIND(cur) == REF_SPHERES) {
       const uint32_t first = REF_INDEX(cur), count = REF_COUNT(cur);
       for (uint32_t k = 0; k < count; k++) {
         const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
         float t;
-        if (sphere_isect(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
+        if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
+          if (t == best.t) {
+            /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
+             * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
+            if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
+              continue;
+            if (__ldg(&sc.msph_meta[first + k].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
+              continue;
+          }
           best.t = t;
           best.prim = MAKE_REF(REF_SPHERES, 1, first + k);
           best.inst = cur_inst;
@@ -166,18 +215,9 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, f
         continue;
       }
     }
-    /* pop */
-    for (;;) {
-      if (sp == 0)
-        return best;
-      cur = stack[--sp];
-      if (cur != TRACE_SENTINEL)
-        break;
-      r = r_in;
-      slab = slab_setup(r);
-      cur_inst = RT_NONE;
-    }
+    cur = pop();
   }
+  return best;
 }
 
 static __device__ __noinline__ TraceHit trace_group_call(const DScene &sc, uint32_t root, const Ray &r, float t_min,

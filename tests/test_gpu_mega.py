@@ -35,7 +35,10 @@ def _batch(sess, desc, golden_file, n=200_000):
     o3, d3 = raygen.secondary_rays(desc, n, seed=202)
     origins = np.concatenate([golden_file["rays_o"], o2, o3])
     dirs = np.concatenate([golden_file["rays_d"], d2, d3])
-    return origins, dirs
+    # d = (0,0,0) is not a ray: the reference's sphere test then returns t = 0/0 = NaN as a "hit" of whatever it
+    # visits first; only the reference-order kernel reproduces that (test_gpu_exact keeps those rays)
+    real = (dirs != 0).any(axis=1)
+    return origins[real], dirs[real]
 
 
 @pytest.mark.parametrize("scene_id", [0, 1, 2, 3, 4, 5, 6])
