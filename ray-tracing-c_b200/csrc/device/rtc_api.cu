@@ -319,6 +319,17 @@ static int enqueue_render(rt_scene *s, const rt_camera *cam, const rt_opts *opts
     CUDA_TRY(cudaEventRecord(s->ev[1], stream));
     CUDA_TRY(mega_render(s->view, job, plan, (float *)s->scratch, stream, &s->last_launches));
     CUDA_TRY(cudaEventRecord(s->ev[2], stream));
+  } else if (opts->kernel == RT_KERNEL_WAVE) {
+    if (!s->mega_ok)
+      return fail(RT_ERR_UNSUPPORTED, "render: %s (use RT_KERNEL_EXACT)", s->mega_why.c_str());
+    WavePlan plan;
+    CUDA_TRY(wave_plan(*cam, count, opts->rng_mode, s->device, &plan));
+    rc = ensure(&s->scratch, &s->scratch_bytes, plan.scratch_bytes);
+    if (rc != RT_OK)
+      return rc;
+    CUDA_TRY(cudaEventRecord(s->ev[1], stream));
+    CUDA_TRY(wave_render(s->view, job, plan, s->scratch, stream, &s->last_launches));
+    CUDA_TRY(cudaEventRecord(s->ev[2], stream));
   } else {
     return fail(RT_ERR_UNSUPPORTED, "render: kernel %u is not available in this build", opts->kernel);
   }

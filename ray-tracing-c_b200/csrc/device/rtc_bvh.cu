@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <set>
@@ -228,8 +229,18 @@ struct Item {
   Box box;
 };
 
-constexpr int kMaxLeaf = 4;
-constexpr float kCostNode = 1.0f, kCostSphere = 0.8f, kCostQuad = 1.4f, kCostInstance = 4.0f;
+/* SAH constants: one inner visit (two box tests) = 1; tunable through the environment for experiments */
+static int env_int(const char *name, int fallback) {
+  const char *v = getenv(name);
+  return v && *v ? atoi(v) : fallback;
+}
+static float env_float(const char *name, float fallback) {
+  const char *v = getenv(name);
+  return v && *v ? (float)atof(v) : fallback;
+}
+static const int kMaxLeaf = std::min(32, std::max(1, env_int("RT_BVH_LEAF", 1)));
+static const float kCostNode = 1.0f, kCostSphere = env_float("RT_BVH_COST_SPHERE", 0.8f),
+                   kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f), kCostInstance = 4.0f;
 
 struct Builder {
   const rt_scene_desc &d;

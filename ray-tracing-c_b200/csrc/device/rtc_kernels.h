@@ -42,6 +42,8 @@ cudaError_t exact_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t st
 /* rtc_mega.cu: persistent megakernel over the rebuilt BVH */
 struct MegaPlan {
   int blocks, threads;   /* persistent grid */
+  int minb;              /* __launch_bounds__ variant: resident CTAs per SM the registers allow */
+  int trav;              /* traversal variant (rtc_trace.cuh) */
   int chunk;             /* samples per work item */
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */
@@ -50,5 +52,18 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
 cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
                         cudaStream_t stream, int *launches);
 cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t stream);
+
+/* rtc_wave.cu: wavefront variant (generate / extend+classify / shade per material queue) over a path-state pool */
+struct WavePlan {
+  MegaPlan mega;        /* chunking of the sample range and the partial-sum buffer (same scheme as the megakernel) */
+  uint32_t slots;       /* path states in the pool */
+  int shade_blocks;     /* grid of each shade launch (grid-stride over its queue) */
+  size_t pool_bytes;    /* SoA pool + queues */
+  size_t scratch_bytes; /* partial sums + pool */
+};
+cudaError_t wave_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, WavePlan *plan);
+/* Blocks the host between batches of iterations (it polls the live-slot count); `stream` is idle on return. */
+cudaError_t wave_render(const DScene &sc, const RenderJob &job, const WavePlan &plan, void *scratch,
+                        cudaStream_t stream, int *launches);
 
 #endif /* RTC_KERNELS_H */

@@ -38,9 +38,24 @@ RTC_DEV V3 v_scale(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 RTC_DEV float v_dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 RTC_DEV float v_len2(V3 a) { return v_dot(a, a); }
 RTC_DEV V3 v_cross(V3 a, V3 b) { return v3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+/* Division and square root of the SHADING code.  IEEE-rounded by default (the exact kernel must match gcc's bits);
+ * a translation unit that defines RTC_FAST_SHADING before including this header (rtc_mega.cu, rtc_wave.cu) gets the
+ * two-instruction approximations instead -- its images are judged by RMSE.  The primitive tests never use these:
+ * they go through the strict s_div / __fsqrt_rn below, so hit distances keep the reference's bits everywhere. */
+#ifdef RTC_FAST_SHADING
+RTC_DEV float f_div(float a, float b) { return __fdividef(a, b); }
+RTC_DEV float f_sqrt(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+#else
+RTC_DEV float f_div(float a, float b) { return __fdiv_rn(a, b); }
+RTC_DEV float f_sqrt(float x) { return __fsqrt_rn(x); }
+#endif
 /* vec3.c:19: division is reciprocal-then-multiply; vec3.c:29 normalises through it */
-RTC_DEV V3 v_div(V3 a, float s) { return v_scale(a, __fdiv_rn(1.0f, s)); }
-RTC_DEV float v_len(V3 a) { return __fsqrt_rn(v_len2(a)); }
+RTC_DEV V3 v_div(V3 a, float s) { return v_scale(a, f_div(1.0f, s)); }
+RTC_DEV float v_len(V3 a) { return f_sqrt(v_len2(a)); }
 RTC_DEV V3 v_unit(V3 a) { return v_div(a, v_len(a)); }
 
 /* ---- strict (never contracted) ---- */

@@ -12,8 +12,10 @@
  * The recursion  colour = emitted + albedo * colour(next) * ratio  is run forwards as  L += beta * emitted;
  * beta *= albedo * ratio  (raytracing.c:57-58,69-71).
  */
+#define RTC_FAST_SHADING /* approximate div/sqrt in the shading code only; see rtc_math.cuh */
 #include "rtc_kernels.h"
 #include "rtc_trace.cuh"
+#include <cstdlib>
 
 #define MEGA_BLOCK 128
 
@@ -28,7 +30,10 @@ RTC_DEV void item_to_pixel(unsigned item_pix, int w, int h, int &i, int &j) {
   j = ty * 4 + (int)(lane >> 3);
 }
 
-__global__ void __launch_bounds__(MEGA_BLOCK)
+/* MINB = resident CTAs per SM the register allocation must allow (occupancy vs spills; chosen from measurements,
+ * RT_MEGA_MINB overrides for tuning) */
+template <int MINB, int TRAV>
+__global__ void __launch_bounds__(MEGA_BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
   const rt_camera &cam = job.cam;
   const int w = cam.img_width, h = cam.img_height;
@@ -119,7 +124,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK)
     th.t = RTC_INF, th.prim = PRIM_NONE, th.inst = RT_NONE;
     if (alive) {
       n_segments++;
-      th = trace_world<false>(sc, ray, 1e-3f, RTC_INF, rng);
+      th = trace_world<false, TRAV>(sc, ray, 1e-3f, RTC_INF, rng);
     }
     __syncwarp();
 
@@ -148,7 +153,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK)
             n_pdf++;
             float sampling_pdf =
                 (1.0f - prob) * scatter_pdf + prob * lights_pdf<false>(sc, sc.lights_root, rec.p, r_out);
-            albedo = v_scale(albedo, __fdiv_rn(scatter_pdf, sampling_pdf));
+            albedo = v_scale(albedo, f_div(scatter_pdf, sampling_pdf));
           }
           beta = v_mul(beta, albedo);
           ray.o = rec.p;
@@ -198,12 +203,38 @@ __global__ void mega_sum_chunks_kernel(const float *__restrict__ partial, float 
   radiance[i] = acc;
 }
 
+typedef void (*MegaKernel)(const DScene, const RenderJob, const MegaPlan, float *);
+static MegaKernel mega_kernel_for(int minb, int trav) {
+  if (trav == 1)
+    return minb == 4 ? mega_render_kernel<4, 1> : minb == 6 ? mega_render_kernel<6, 1> : mega_render_kernel<8, 1>;
+  return minb == 4 ? mega_render_kernel<4, 0> : minb == 6 ? mega_render_kernel<6, 0> : mega_render_kernel<8, 0>;
+}
+static int mega_trav() { /* 0 = while-while, 1 = leaves intersected inside the node loop */
+  static int cached = -1;
+  if (cached < 0) {
+    const char *v = getenv("RT_MEGA_TRAV");
+    cached = v ? (atoi(v) == 1 ? 1 : 0) : 0;
+  }
+  return cached;
+}
+static int mega_minb() {
+  static int cached = 0;
+  if (cached == 0) {
+    const char *v = getenv("RT_MEGA_MINB");
+    int m = v ? atoi(v) : 8;
+    cached = (m == 4 || m == 6 || m == 8) ? m : 8;
+  }
+  return cached;
+}
+
 cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, MegaPlan *plan) {
   int sms = 0, per_sm = 0;
   cudaError_t err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (err != cudaSuccess)
     return err;
-  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mega_render_kernel, MEGA_BLOCK, 0);
+  plan->minb = mega_minb();
+  plan->trav = mega_trav();
+  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mega_kernel_for(plan->minb, plan->trav), MEGA_BLOCK, 0);
   if (err != cudaSuccess)
     return err;
   if (per_sm < 1)
@@ -232,7 +263,7 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
 
 cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
                         cudaStream_t stream, int *launches) {
-  mega_render_kernel<<<plan.blocks, plan.threads, 0, stream>>>(sc, job, plan, partial);
+  mega_kernel_for(plan.minb, plan.trav)<<<plan.blocks, plan.threads, 0, stream>>>(sc, job, plan, partial);
   cudaError_t err = cudaGetLastError();
   *launches = 1;
   if (err != cudaSuccess)
@@ -249,7 +280,7 @@ cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &
 
 /* ------------------------------------------------------------------ rt_hit_batch over the rebuilt BVH ---- */
 
-__global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kernel(const DScene sc, const HitBatch b) {
+template <int TRAV> __global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kernel(const DScene sc, const HitBatch b) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= b.n)
     return;
@@ -261,7 +292,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kernel(const DScene sc, c
     g.state = b.rng_io[2 * i];
     g.inc = b.rng_io[2 * i + 1];
   }
-  TraceHit th = trace_world<true>(sc, ray, b.t_min, b.t_max, g);
+  TraceHit th = trace_world<true, TRAV>(sc, ray, b.t_min, b.t_max, g);
   if (b.rng_io)
     b.rng_io[2 * i] = g.state;
   const bool hit = th.prim != PRIM_NONE;
@@ -288,6 +319,9 @@ cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t str
   if (b.n == 0)
     return cudaSuccess;
   unsigned blocks = (unsigned)((b.n + MEGA_BLOCK - 1) / MEGA_BLOCK);
-  mega_hit_kernel<<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
+  if (mega_trav() == 1)
+    mega_hit_kernel<1><<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
+  else
+    mega_hit_kernel<0><<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
   return cudaGetLastError();
 }

@@ -99,7 +99,7 @@ RTC_DEV V3 rng_unit_vector(Rng &g) {
     V3 c = v3(x, y, z);
     float l2 = v_len2(c);
     if (l2 < 1.0f)
-      return v_div(c, __fsqrt_rn(l2));
+      return v_div(c, f_sqrt(l2));
   }
 }
 
@@ -139,7 +139,8 @@ RTC_DEV float perlin_turbulence(const rt_perlin *pl, int depth, V3 p) { /* textu
   return fabsf(value);
 }
 
-template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, float u, float v, V3 p) {
+/* everything but a solid colour: out of line, so that the hot shading code stays small in the instruction cache */
+template <bool EXACT> __device__ __noinline__ V3 texture_value_slow(const DScene &sc, uint32_t id, float u, float v, V3 p) {
   for (;;) {
     const rt_texture *t = &sc.textures[id];
     uint32_t kind = __ldg(&t->kind);
@@ -147,7 +148,7 @@ template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, fl
       return v3(__ldg(&t->color[0]), __ldg(&t->color[1]), __ldg(&t->color[2]));
     if (kind == RT_TEX_CHECKER) { /* texture.c:12-22: on (u,v); % keeps the sign, so -1 selects `odd` too */
       float scale = __ldg(&t->scale);
-      int iu = (int)floorf(__fdiv_rn(u, scale)), iv = (int)floorf(__fdiv_rn(v, scale));
+      int iu = (int)floorf(f_div(u, scale)), iv = (int)floorf(f_div(v, scale));
       id = ((iu + iv) % 2) ? __ldg(&t->b) : __ldg(&t->a);
       continue;
     }
@@ -159,8 +160,8 @@ template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, fl
       int i = (fi >= 0.0f) ? (fi <= (float)(w - 1) ? (int)fi : w - 1) : 0; /* NaN -> 0 */
       int j = (fj >= 0.0f) ? (fj <= (float)(h - 1) ? (int)fj : h - 1) : 0;
       const uint8_t *px = sc.texels + im->offset + ((size_t)j * w + i) * 3;
-      return v3(__fdiv_rn((float)__ldg(px), 255.0f), __fdiv_rn((float)__ldg(px + 1), 255.0f),
-                __fdiv_rn((float)__ldg(px + 2), 255.0f));
+      return v3(f_div((float)__ldg(px), 255.0f), f_div((float)__ldg(px + 1), 255.0f),
+                f_div((float)__ldg(px + 2), 255.0f));
     }
     if (kind == RT_TEX_PERLIN) { /* texture.c:47-52 */
       V3 q = v_scale(p, __ldg(&t->scale));
@@ -170,6 +171,13 @@ template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, fl
     }
     return v3(0, 0, 0);
   }
+}
+
+template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, float u, float v, V3 p) {
+  const rt_texture *t = &sc.textures[id];
+  if (__ldg(&t->kind) == RT_TEX_SOLID) /* texture.c:8 */
+    return v3(__ldg(&t->color[0]), __ldg(&t->color[1]), __ldg(&t->color[2]));
+  return texture_value_slow<EXACT>(sc, id, u, v, p);
 }
 
 /* does evaluating this texture read (u, v)?  (lets the fast kernels skip atan2f/acosf on spheres) */
@@ -200,8 +208,8 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
     float phi = 2.0f * RTC_PI * r1;
     float sn, cs;
     m_sincos<EXACT>(phi, &sn, &cs);
-    float sr2 = __fsqrt_rn(r2);
-    V3 local = v3(cs * sr2, sn * sr2, __fsqrt_rn(1.0f - r2));
+    float sr2 = f_sqrt(r2);
+    V3 local = v3(cs * sr2, sn * sr2, f_sqrt(1.0f - r2));
     r_out = basis_local(b, local);
     albedo = texture_value<EXACT>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p);
     skip_pdf = false;
@@ -219,18 +227,18 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
   case RT_MAT_DIELECTRIC: { /* material.c:62-86 */
     float eta = __ldg(&m->param);
     if (rec.front)
-      eta = __fdiv_rn(1.0f, eta);
+      eta = f_div(1.0f, eta);
     V3 in = v_unit(r_in);
     float cos_theta = fminf(-v_dot(in, rec.n), 1.0f);
-    float sin_theta = __fsqrt_rn(1.0f - cos_theta * cos_theta);
-    float schlick = __fdiv_rn(1.0f - eta, 1.0f + eta);
+    float sin_theta = f_sqrt(1.0f - cos_theta * cos_theta);
+    float schlick = f_div(1.0f - eta, 1.0f + eta);
     schlick *= schlick;
     schlick += (1.0f - schlick) * pm_pow5f(1.0f - cos_theta);
     if (eta * sin_theta > 1.0f || schlick > rng_f32(g)) { /* the draw is skipped on total internal reflection */
       r_out = reflect(in, rec.n);
     } else {
       V3 perp = v_scale(v_add(in, v_scale(rec.n, cos_theta)), eta);
-      V3 para = v_scale(rec.n, -__fsqrt_rn(fabsf(1.0f - v_len2(perp))));
+      V3 para = v_scale(rec.n, -f_sqrt(fabsf(1.0f - v_len2(perp))));
       r_out = v_add(perp, para);
     }
     albedo = v3(1, 1, 1);
@@ -252,10 +260,10 @@ RTC_DEV float material_scatter_pdf(const DScene &sc, uint32_t material, V3 norma
   uint32_t tag = __ldg(&sc.materials[material].tag);
   if (tag == RT_MAT_LAMBERTIAN) {
     float cos_theta = v_dot(normal, v_unit(r_out));
-    return cos_theta < 0.0f ? 0.0f : __fdiv_rn(cos_theta, RTC_PI);
+    return cos_theta < 0.0f ? 0.0f : f_div(cos_theta, RTC_PI);
   }
   if (tag == RT_MAT_ISOTROPIC)
-    return __fdiv_rn(1.0f, 4.0f * RTC_PI);
+    return f_div(1.0f, 4.0f * RTC_PI);
   return 0.0f;
 }
 
@@ -278,20 +286,20 @@ template <bool EXACT> RTC_DEV float sphere_pdf(const rt_sphere &s, V3 o, V3 d) {
   if (!sphere_hit<EXACT>(s, o, d, 0.001f, RTC_INF, rec))
     return 0.0f;
   V3 oc = v_sub(v_load(s.center), o);
-  float cos_max = __fsqrt_rn(1.0f - __fdiv_rn(s.radius * s.radius, v_len2(oc)));
+  float cos_max = f_sqrt(1.0f - f_div(s.radius * s.radius, v_len2(oc)));
   float solid_angle = 2.0f * RTC_PI * (1.0f - cos_max);
-  return __fdiv_rn(1.0f, solid_angle);
+  return f_div(1.0f, solid_angle);
 }
 template <bool EXACT> RTC_DEV V3 sphere_rand(const rt_sphere &s, V3 origin, Rng &g) { /* hittable.c:163-178 */
   V3 oc = v_sub(v_load(s.center), origin);
   float r1 = rng_f32(g);
   float r2 = rng_f32(g);
-  float z = 1.0f + r2 * (__fsqrt_rn(1.0f - __fdiv_rn(s.radius * s.radius, v_len2(oc))) - 1.0f);
+  float z = 1.0f + r2 * (f_sqrt(1.0f - f_div(s.radius * s.radius, v_len2(oc))) - 1.0f);
   float phi = 2.0f * RTC_PI * r1;
   float sn, cs;
   m_sincos<EXACT>(phi, &sn, &cs);
-  float x = cs * __fsqrt_rn(1.0f - z * z);
-  float y = sn * __fsqrt_rn(1.0f - z * z);
+  float x = cs * f_sqrt(1.0f - z * z);
+  float y = sn * f_sqrt(1.0f - z * z);
   Basis b = basis_from_w(oc);
   return basis_local(b, v3(x, y, z));
 }
@@ -301,7 +309,7 @@ RTC_DEV float quad_pdf(const rt_quad &q, V3 o, V3 d) { /* hittable.c:215-224 */
     return 0.0f;
   float d2 = rec.t * rec.t * v_len2(d);
   float cos_theta = fabsf(v_dot(rec.n, v_unit(d)));
-  return __fdiv_rn(d2, cos_theta * q.area);
+  return f_div(d2, cos_theta * q.area);
 }
 RTC_DEV V3 quad_rand(const rt_quad &q, V3 origin, Rng &g) { /* hittable.c:225-228; gcc draws v's coefficient first */
   float along_v = rng_f32(g);
@@ -313,7 +321,7 @@ RTC_DEV V3 quad_rand(const rt_quad &q, V3 origin, Rng &g) { /* hittable.c:225-22
 #define RTC_LIGHT_NESTING 4 /* lists inside the lights list, checked by rt_scene_create */
 
 /* hittable.c:89-100: mean over the items that have a pdf; nested lists recurse */
-template <bool EXACT> RTC_DEV float lights_pdf(const DScene &sc, uint32_t root, V3 o, V3 d) {
+template <bool EXACT> __device__ __noinline__ float lights_pdf(const DScene &sc, uint32_t root, V3 o, V3 d) {
   uint32_t st_node[RTC_LIGHT_NESTING], st_idx[RTC_LIGHT_NESTING];
   float st_sum[RTC_LIGHT_NESTING], st_cnt[RTC_LIGHT_NESTING];
   int sp = 0;
@@ -344,7 +352,7 @@ template <bool EXACT> RTC_DEV float lights_pdf(const DScene &sc, uint32_t root, 
       st_sum[sp] += pdf;
       st_cnt[sp] += 1.0f;
     } else {
-      ret = __fdiv_rn(st_sum[sp], fmaxf(st_cnt[sp], 1.0f));
+      ret = f_div(st_sum[sp], fmaxf(st_cnt[sp], 1.0f));
       if (sp == 0)
         return ret;
       sp--;
@@ -355,7 +363,7 @@ template <bool EXACT> RTC_DEV float lights_pdf(const DScene &sc, uint32_t root, 
 }
 
 /* hittable.c:101-107: uniform item, retry while the item has no `rand`; nested lists descend */
-template <bool EXACT> RTC_DEV V3 lights_rand(const DScene &sc, uint32_t root, V3 origin, Rng &g) {
+template <bool EXACT> __device__ __noinline__ V3 lights_rand(const DScene &sc, uint32_t root, V3 origin, Rng &g) {
   uint32_t id = root;
   for (;;) {
     const rt_node *n = &sc.nodes[id];

@@ -57,6 +57,7 @@ struct TraceHit {
 
 struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * inv (one FMA per plane) */
   V3 inv, oi;
+  float slack; /* bound on the rounding error of an interval comparison made with those t's */
 };
 RTC_DEV SlabRay slab_setup(const Ray &r) {
   SlabRay s;
@@ -69,6 +70,11 @@ RTC_DEV SlabRay slab_setup(const Ray &r) {
              r.d.y == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.y), 1e30f), r.d.y),
              r.d.z == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.z), 1e30f), r.d.z));
   s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
+  /* plane*inv - o*inv cancels: each t carries an ABSOLUTE error of about eps * |o*inv| (o*inv and inv are already
+   * rounded), which for coordinates in the hundreds is as large as the reference's 1e-4 padding of flat boxes.  Two
+   * such errors meet in `enter <= leave`, so the exit distance is widened by 3e-7 * max|o*inv| (NaN axes drop out):
+   * a box the exact ray touches is never culled. */
+  s.slack = 3e-7f * fmaxf(fmaxf(fabsf(s.oi.x), fabsf(s.oi.y)), fabsf(s.oi.z));
   return s;
 }
 
@@ -81,7 +87,7 @@ RTC_DEV float slab_entry(const SlabRay &s, float xlo, float xhi, float ylo, floa
   float z0 = fmaf(zlo, s.inv.z, -s.oi.z), z1 = fmaf(zhi, s.inv.z, -s.oi.z);
   float enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
   float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
-  leave = fmaf(fabsf(leave), 4e-7f, leave); /* two ulps of slack: never cull a hit the reference would find */
+  leave = fmaf(fabsf(leave), 4e-7f, leave) + s.slack; /* relative + absolute slack: never cull a true hit */
   return enter <= leave ? enter : RTC_INF;
 }
 
@@ -103,6 +109,61 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float t_mi
   }
   *t = root;
   return true;
+}
+
+/* Intersects the primitives of one leaf reference (spheres or quads) and keeps the closest; ties as the reference. */
+RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float t_min, uint32_t cur_inst, TraceHit &best,
+                            uint32_t &best_node) {
+  if (REF_KIND(ref) == REF_SPHERES) {
+    const uint32_t first = REF_INDEX(ref), count = REF_COUNT(ref);
+    for (uint32_t k = 0; k < count; k++) {
+      const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
+      float t;
+      if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
+        if (t == best.t) {
+          /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
+           * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
+          if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
+            continue;
+          if (__ldg(&sc.msph_meta[first + k].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
+            continue;
+        }
+        best.t = t;
+        best.prim = MAKE_REF(REF_SPHERES, 1, first + k);
+        best.inst = cur_inst;
+      }
+    }
+  } else if (REF_KIND(ref) == REF_QUADS) {
+    const uint32_t first = REF_INDEX(ref), count = REF_COUNT(ref);
+    for (uint32_t k = 0; k < count; k++) {
+      const MQuad *q = &sc.mquads[first + k];
+      const float4 n_D = __ldg(&q->n_D);
+      /* plane distance first: most candidates die here, before the other four rows are read */
+      V3 nrm = v3(n_D.x, n_D.y, n_D.z);
+      float denom = sv_dot(nrm, r.d);
+      if (fabsf(denom) < 1e-8f)
+        continue;
+      float tt = s_div(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
+      if (tt < t_min || tt > best.t)
+        continue;
+      const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
+      V3 hp = sv_sub(sv_at(r.o, r.d, tt), v3(q_mat.x, q_mat.y, q_mat.z));
+      V3 w = v3(w_nod.x, w_nod.y, w_nod.z);
+      float al = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
+      float be = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
+      if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
+        continue;
+      const uint32_t node = __float_as_uint(w_nod.w);
+      /* exact tie with an earlier candidate: the reference keeps the LATER-visited quad (closed interval,
+       * hittable.c:194) and a quad always displaces a sphere at equal t; node ids are its visiting order */
+      if (tt == best.t && best.prim != PRIM_NONE && REF_KIND(best.prim) == REF_QUADS && node < best_node)
+        continue;
+      best.t = tt;
+      best.prim = MAKE_REF(REF_QUADS, 1, first + k);
+      best.inst = cur_inst;
+      best_node = node;
+    }
+  }
 }
 
 /* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame). */
@@ -155,55 +216,8 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, f
     }
     if (cur == REF_EMPTY)
       break;
-    if (REF_KIND(cur) == REF_SPHERES) {
-      const uint32_t first = REF_INDEX(cur), count = REF_COUNT(cur);
-      for (uint32_t k = 0; k < count; k++) {
-        const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
-        float t;
-        if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
-          if (t == best.t) {
-            /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
-             * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
-            if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
-              continue;
-            if (__ldg(&sc.msph_meta[first + k].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
-              continue;
-          }
-          best.t = t;
-          best.prim = MAKE_REF(REF_SPHERES, 1, first + k);
-          best.inst = cur_inst;
-        }
-      }
-    } else if (REF_KIND(cur) == REF_QUADS) {
-      const uint32_t first = REF_INDEX(cur), count = REF_COUNT(cur);
-      for (uint32_t k = 0; k < count; k++) {
-        const MQuad *q = &sc.mquads[first + k];
-        const float4 n_D = __ldg(&q->n_D);
-        /* plane distance first: most candidates die here, before the other four rows are read */
-        V3 nrm = v3(n_D.x, n_D.y, n_D.z);
-        float denom = sv_dot(nrm, r.d);
-        if (fabsf(denom) < 1e-8f)
-          continue;
-        float tt = s_div(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
-        if (tt < t_min || tt > best.t)
-          continue;
-        const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
-        V3 hp = sv_sub(sv_at(r.o, r.d, tt), v3(q_mat.x, q_mat.y, q_mat.z));
-        V3 w = v3(w_nod.x, w_nod.y, w_nod.z);
-        float al = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
-        float be = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
-        if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
-          continue;
-        const uint32_t node = __float_as_uint(w_nod.w);
-        /* exact tie with an earlier candidate: the reference keeps the LATER-visited quad (closed interval,
-         * hittable.c:194) and a quad always displaces a sphere at equal t; node ids are its visiting order */
-        if (tt == best.t && best.prim != PRIM_NONE && REF_KIND(best.prim) == REF_QUADS && node < best_node)
-          continue;
-        best.t = tt;
-        best.prim = MAKE_REF(REF_QUADS, 1, first + k);
-        best.inst = cur_inst;
-        best_node = node;
-      }
+    if (REF_KIND(cur) != REF_INSTANCE) {
+      leaf_intersect(sc, cur, r, t_min, cur_inst, best, best_node);
     } else { /* instance: enter its frame; a sentinel on the stack brings the outer ray back */
       const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
       if (inst.z != REF_EMPTY) {
@@ -218,6 +232,85 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, f
     cur = pop();
   }
   return best;
+}
+
+/* Variant: primitive leaves are intersected INSIDE the node loop, the moment their box is hit, so a lane never waits
+ * for the rest of its warp to reach a leaf; the stack holds inner nodes (and instances) only.  Same results. */
+RTC_DEV TraceHit trace_group_inline(const DScene &sc, uint32_t root, const Ray &r_in, float t_min, float t_max) {
+  TraceHit best;
+  best.t = t_max, best.prim = PRIM_NONE, best.inst = RT_NONE;
+  if (root == REF_EMPTY)
+    return best;
+
+  uint32_t stack[TRACE_STACK];
+  int sp = 0;
+  Ray r = r_in;
+  SlabRay slab = slab_setup(r);
+  uint32_t cur = root, cur_inst = RT_NONE;
+  uint32_t best_node = 0;
+
+  auto pop = [&]() -> uint32_t {
+    for (;;) {
+      if (sp == 0)
+        return REF_EMPTY;
+      uint32_t c = stack[--sp];
+      if (c != TRACE_SENTINEL)
+        return c;
+      r = r_in;
+      slab = slab_setup(r);
+      cur_inst = RT_NONE;
+    }
+  };
+
+  while (cur != REF_EMPTY) {
+    if (REF_KIND(cur) != REF_INNER) { /* only a group/instance root or a deferred instance arrives here */
+      if (REF_KIND(cur) == REF_INSTANCE) {
+        const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
+        if (inst.z != REF_EMPTY) {
+          stack[sp++] = TRACE_SENTINEL;
+          cur_inst = REF_INDEX(cur);
+          r = chain_apply(sc, inst.x, inst.y, r_in);
+          slab = slab_setup(r);
+          cur = inst.z;
+          continue;
+        }
+      } else {
+        leaf_intersect(sc, cur, r, t_min, cur_inst, best, best_node);
+      }
+      cur = pop();
+      continue;
+    }
+    const BNode *n = &sc.bnodes[REF_INDEX(cur)];
+    const float4 xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
+    const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(&n->child0));
+    float e0 = slab_entry(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t);
+    float e1 = slab_entry(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t);
+    const bool swap = e1 < e0;
+    uint32_t c_near = swap ? ch.y : ch.x, c_far = swap ? ch.x : ch.y;
+    float e_near = swap ? e1 : e0, e_far = swap ? e0 : e1;
+    uint32_t next = REF_EMPTY;
+#pragma unroll 1
+    for (int k = 0; k < 2; k++) { /* near child, then far child (one copy of the leaf code) */
+      const uint32_t c = k ? c_far : c_near;
+      const float e = k ? e_far : e_near;
+      if (!(e < RTC_INF) || e > best.t) /* missed, or a closer hit was found meanwhile */
+        continue;
+      const uint32_t kind = REF_KIND(c);
+      if (kind == REF_SPHERES || kind == REF_QUADS) {
+        leaf_intersect(sc, c, r, t_min, cur_inst, best, best_node);
+      } else if (next == REF_EMPTY) {
+        next = c;
+      } else {
+        stack[sp++] = c;
+      }
+    }
+    cur = next != REF_EMPTY ? next : pop();
+  }
+  return best;
+}
+
+template <int TRAV> RTC_DEV TraceHit trace_group_mode(const DScene &sc, uint32_t root, const Ray &r, float t_min, float t_max) {
+  return TRAV == 1 ? trace_group_inline(sc, root, r, t_min, t_max) : trace_group(sc, root, r, t_min, t_max);
 }
 
 static __device__ __noinline__ TraceHit trace_group_call(const DScene &sc, uint32_t root, const Ray &r, float t_min,
@@ -306,8 +399,9 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
 }
 
 /* The integrator's query (raytracing.c:45): surfaces, then media. */
-template <bool EXACT> RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
-  TraceHit best = trace_group(sc, sc.world_root, world, t_min, t_max);
+template <bool EXACT, int TRAV = 0>
+RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
+  TraceHit best = trace_group_mode<TRAV>(sc, sc.world_root, world, t_min, t_max);
   if (sc.n_media)
     trace_media<EXACT>(sc, world, t_min, best, g);
   return best;

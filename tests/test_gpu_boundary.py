@@ -70,6 +70,28 @@ def test_cli_writes_the_reference_tiff(rtc, scene_factory):
         assert proc.returncode == 0, proc.stderr
 
 
+def test_reference_main_c_runs_on_the_backend_unchanged(rtc, scene_factory):
+    """oracle/_ref/main_dropin = the reference's OWN src/main.c (scene builders, CLI, timing, TIFF call), compiled
+    unchanged against include/*.h and linked to librtc_host.so + librtc_b200.so (option A).  Its
+    output.tiff must carry the image this backend renders for the same scene."""
+    from conftest import ROOT
+
+    exe = ROOT / "oracle" / "_ref" / "main_dropin"
+    if not exe.exists():
+        pytest.skip("oracle/_ref/main_dropin not built (needs /root/reference at build time)")
+    with tempfile.TemporaryDirectory() as tmp:
+        env = dict(os.environ, RT_KERNEL="exact", RT_RNG="pixel")
+        proc = subprocess.run([str(exe), "6", "40", "2", "x"], cwd=tmp, capture_output=True, text=True, env=env)
+        assert proc.returncode == 0, proc.stderr
+        data = (Path(tmp) / "output.tiff").read_bytes()
+    sess, desc = scene_factory(6, 40, 2)
+    payload = np.frombuffer(data[-sess.width * sess.height * 3:], dtype=np.uint8).reshape(sess.height, sess.width, 3)
+    scene = rtc.Scene(desc)
+    rgb, _, _ = scene.render(sess.camera, rtc.make_opts(kernel="exact", rng="pixel"))
+    scene.close()
+    assert np.array_equal(payload, rgb)
+
+
 def test_render_multi_one_gpu_equals_render(rtc, scene_factory):
     sess, desc = scene_factory(5, 64, 16)
     opts = rtc.make_opts(kernel="mega", rng="sample")

@@ -129,6 +129,49 @@ def test_render_rmse_against_oracle(rtc, oracle, gpu_scene, scene_id):
     assert abs(st_m["segments"] - st_o["segments"]) <= 0.02 * st_o["segments"]
 
 
+@pytest.mark.parametrize("scene_id", range(8))
+def test_wavefront_render_rmse_against_oracle(rtc, oracle, gpu_scene, scene_id):
+    """RT_KERNEL_WAVE (generate / extend+classify / shade-per-material queues) under the same bar as the megakernel,
+    plus: it traces the same number of camera samples and (within fast-math forks) the same segments as the
+    megakernel, and the two images agree far inside the noise."""
+    width, spp = (64, 16) if scene_id != 7 else (48, 16)
+    sess, desc, scene = gpu_scene(scene_id, width, spp)
+    cam = sess.camera
+    _, rad_o, st_o = oracle.render(desc, cam, rtc.make_opts(kernel="exact", rng="sample"), oracle.MATH_PORTABLE)
+    _, rad_p, _ = oracle.render(desc, cam, rtc.make_opts(kernel="exact", rng="pixel"), oracle.MATH_PORTABLE)
+    _, rad_w, st_w = scene.render(cam, rtc.make_opts(kernel="wave", rng="sample"))
+    _, rad_m, st_m = scene.render(cam, rtc.make_opts(kernel="mega", rng="sample"))
+    img_o, img_p, img_w, img_m = rad_o / spp, rad_p / spp, rad_w / spp, rad_m / spp
+    ok = np.isfinite(img_o).all(axis=2) & np.isfinite(img_w).all(axis=2) & np.isfinite(img_p).all(axis=2) & \
+        np.isfinite(img_m).all(axis=2)
+    assert ok.mean() > 0.99
+    img_o, img_p, img_w, img_m = (np.where(ok[..., None], x, 0.0) for x in (img_o, img_p, img_w, img_m))
+    floor = _rmse(img_o, img_p)
+    assert (_rmse(img_w, img_o) <= 0.5 * floor + 1e-4).all(), (_rmse(img_w, img_o), floor)
+    assert (_rmse(img_w, img_m) <= 0.25 * floor + 1e-4).all()
+    bias = np.abs(np.clip(img_w, 0, 1).mean(axis=(0, 1)) - np.clip(img_o, 0, 1).mean(axis=(0, 1)))
+    assert (bias <= 2.0 / 255.0).all(), bias
+    assert st_w["samples"] == st_o["samples"]
+    assert abs(st_w["segments"] - st_o["segments"]) <= 0.02 * st_o["segments"]
+    assert st_w["launches"] > 8
+
+
+def test_wavefront_is_deterministic_and_handles_pixel_streams(rtc, oracle, gpu_scene):
+    sess, desc, scene = gpu_scene(1, 96, 32)
+    cam = sess.camera
+    opts = rtc.make_opts(kernel="wave", rng="sample")
+    _, a, st_a = scene.render(cam, opts)
+    _, b, st_b = scene.render(cam, opts)
+    assert same_bits(a, b).all() and st_a["segments"] == st_b["segments"]
+    _, lo, _ = scene.render(cam, rtc.make_opts(kernel="wave", rng="sample", sample_begin=0, sample_count=20))
+    _, hi, _ = scene.render(cam, rtc.make_opts(kernel="wave", rng="sample", sample_begin=20, sample_count=12))
+    assert np.allclose(lo + hi, a, rtol=2e-5, atol=1e-5)
+    _, rad_px, _ = scene.render(cam, rtc.make_opts(kernel="wave", rng="pixel"))
+    _, rad_o, _ = oracle.render(desc, cam, rtc.make_opts(kernel="exact", rng="pixel"), oracle.MATH_PORTABLE)
+    _, rad_s, _ = oracle.render(desc, cam, rtc.make_opts(kernel="exact", rng="sample"), oracle.MATH_PORTABLE)
+    assert (_rmse(rad_px / 32, rad_o / 32) <= 0.6 * _rmse(rad_s / 32, rad_o / 32) + 1e-4).all()
+
+
 def test_pixel_rng_mode_on_mega(rtc, oracle, gpu_scene):
     """RT_RNG_PIXEL (the reference's own contract: one stream per pixel) also runs on the throughput kernel."""
     sess, desc, scene = gpu_scene(1, 64, 16)
