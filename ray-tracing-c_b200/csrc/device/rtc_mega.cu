@@ -247,13 +247,16 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   if (rng_mode == RT_RNG_SAMPLE && pixels > 0) {
     /* enough items that the end-of-kernel tail (lanes waiting for the last items) stays small, but chunks of at
      * least 8 samples so the per-item store and fetch are noise */
-    long long want = (24 * lanes + pixels - 1) / pixels;
+    long long want = (64 * lanes + pixels - 1) / pixels;
     long long most = sample_count / 8;
     n_chunks = (int)(want < 1 ? 1 : want);
     if (n_chunks > most)
       n_chunks = (int)(most < 1 ? 1 : most);
     if (n_chunks > 64)
       n_chunks = 64;
+    const char *env = getenv("RT_MEGA_CHUNKS"); /* tuning */
+    if (env && atoi(env) > 0 && atoi(env) <= sample_count)
+      n_chunks = atoi(env);
   }
   plan->chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->n_chunks = plan->chunk > 0 ? (sample_count + plan->chunk - 1) / plan->chunk : 1;
