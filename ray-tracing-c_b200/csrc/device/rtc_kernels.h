@@ -43,7 +43,9 @@ cudaError_t exact_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t st
 struct MegaPlan {
   int blocks, threads;   /* persistent grid */
   int minb;              /* __launch_bounds__ variant: resident CTAs per SM the registers allow */
-  int trav;              /* traversal variant (rtc_trace.cuh) */
+  int nv;                /* paths per lane: 0 = register kernel, else the warp-ray-queue kernel (rtc_mega.cu) */
+  int variant;           /* index into rtc_mega.cu's table of built kernels */
+  int thr8;              /* node loop runs while >= thr8/8 of the busy lanes want it (walk_round_sync) */
   int chunk;             /* samples per work item */
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */

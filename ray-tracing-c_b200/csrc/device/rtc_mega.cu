@@ -2,15 +2,23 @@
  * rtc_mega.cu -- RT_KERNEL_MEGA: the persistent megakernel (throughput path).
  *
  * Replaces the loop nest of Camera_render + Camera_ray_color (/root/reference/src/raytracing.c:39-133).
- * One CTA set sized to the machine (SM count x resident CTAs) stays resident; every lane owns one path at a time
- * and, the moment its path ends, regenerates: next sample of its work item, or a new work item fetched from a
- * global counter.  So every trip of the main loop is "one segment for 32 lanes" -- no lane idles on a finished
- * path, which is what depth-50 tails (dielectrics) would otherwise cost.
+ * One CTA set sized to the machine (SM count x resident CTAs) stays resident; a path that ends is regenerated on the
+ * spot: next sample of its work item, or a new work item fetched from a global counter.  So every trip of the main
+ * loop is "one segment for every path" -- nothing idles on a finished path, which is what depth-50 tails
+ * (dielectrics) would otherwise cost.
  *
- * Work item = (pixel, sample chunk).  A lane sums its chunk in registers and stores the partial sum once; chunks
+ * Work item = (pixel, sample chunk).  Its samples are summed privately and the partial sum is stored once; chunks
  * of a pixel are added up in chunk order by a second tiny kernel, so the image is deterministic (no float atomics).
  * The recursion  colour = emitted + albedo * colour(next) * ratio  is run forwards as  L += beta * emitted;
  * beta *= albedo * ratio  (raytracing.c:57-58,69-71).
+ *
+ * Two kernels share the per-path code (camera ray, shading):
+ *   mega_render_kernel  one path per lane, state in registers, one ray per lane per trip.
+ *   mega_queue_kernel   NV paths per lane ("virtual lanes"), state in shared memory, and the trip's NV*32 rays of a
+ *                       warp are handed to its 32 lanes DYNAMICALLY: a lane that finishes a short ray takes the next
+ *                       ray of the warp's queue instead of waiting for the longest ray of the trip.  ncu on the
+ *                       one-path kernel (Book 1): 31 node-loop iterations per trip against a mean of 10.8 visits
+ *                       per ray -- two thirds of the lane-slots of the dominant loop idle behind the longest ray.
  */
 #define RTC_FAST_SHADING /* approximate div/sqrt in the shading code only; see rtc_math.cuh */
 #include "rtc_kernels.h"
@@ -18,6 +26,8 @@
 #include <cstdlib>
 
 #define MEGA_BLOCK 128
+#define MEGA_NV_DEFAULT 0   /* measured: see DESIGN.md */
+#define MEGA_THR8_DEFAULT 2 /* measured: see DESIGN.md */
 
 RTC_DEV bool has_nan3(V3 a) { return a.x != a.x || a.y != a.y || a.z != a.z; }
 
@@ -30,153 +40,101 @@ RTC_DEV void item_to_pixel(unsigned item_pix, int w, int h, int &i, int &j) {
   j = ty * 4 + (int)(lane >> 3);
 }
 
-/* MINB = resident CTAs per SM the register allocation must allow (occupancy vs spills; chosen from measurements,
- * RT_MEGA_MINB overrides for tuning) */
-template <int MINB, int TRAV>
-__global__ void __launch_bounds__(MEGA_BLOCK, MINB)
-    mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
+/* what every path of a render shares (kernel-uniform) */
+struct Frame {
+  int w, h, max_depth;
+  unsigned tiles, n_items;
+  V3 px00, du, dv, eye, lens_u, lens_v, background;
+  float prob, dof_angle;
+  bool use_lights;
+};
+RTC_DEV Frame frame_of(const DScene &sc, const RenderJob &job, const MegaPlan &plan) {
   const rt_camera &cam = job.cam;
-  const int w = cam.img_width, h = cam.img_height;
-  const unsigned tiles = (unsigned)(((w + 7) >> 3) * ((h + 3) >> 2));
-  const unsigned n_items = tiles * 32u * (unsigned)plan.n_chunks;
-  const V3 px00 = v_load(cam.pixel00), du = v_load(cam.pixel_delta_u), dv = v_load(cam.pixel_delta_v);
-  const V3 eye = v_load(cam.origin), lens_u = v_load(cam.dof_disc_u), lens_v = v_load(cam.dof_disc_v);
-  const V3 background = v_load(cam.background);
-  const float prob = cam.lights_sampling_prob;
-  const bool use_lights = !(prob == 0.0f || sc.lights_root == RT_NONE);
-  const int max_depth = cam.max_depth;
+  Frame f;
+  f.w = cam.img_width, f.h = cam.img_height, f.max_depth = cam.max_depth;
+  f.tiles = (unsigned)(((f.w + 7) >> 3) * ((f.h + 3) >> 2));
+  f.n_items = f.tiles * 32u * (unsigned)plan.n_chunks;
+  f.px00 = v_load(cam.pixel00), f.du = v_load(cam.pixel_delta_u), f.dv = v_load(cam.pixel_delta_v);
+  f.eye = v_load(cam.origin), f.lens_u = v_load(cam.dof_disc_u), f.lens_v = v_load(cam.dof_disc_v);
+  f.background = v_load(cam.background);
+  f.prob = cam.lights_sampling_prob, f.dof_angle = cam.dof_angle;
+  f.use_lights = !(f.prob == 0.0f || sc.lights_root == RT_NONE);
+  return f;
+}
 
-  unsigned long long n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
-
-  /* per-lane path state */
-  Rng rng;
-  rng.state = 0, rng.inc = 1;
-  Ray ray;
-  ray.o = ray.d = v3(0, 0, 0);
-  V3 beta = v3(1, 1, 1), L = v3(0, 0, 0), sum = v3(0, 0, 0), pixel = v3(0, 0, 0);
-  int pi = 0, pj = 0, s = 0, s_end = 0, depth = 0, chunk_id = 0;
-  bool have_item = false, alive = false;
-
-  bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
+/* Fetches the next work item that lies inside the image.  false = no items left. */
+RTC_DEV bool fetch_item(const Frame &f, const RenderJob &job, int &pi, int &pj, int &chunk_id) {
   for (;;) {
-    /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
-    if (!alive && !done) {
-      if (have_item && s == s_end) { /* chunk finished: one store per item */
-        float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)w * h * 3 : job.radiance) +
-                     ((size_t)pj * w + pi) * 3;
-        dst[0] = sum.x, dst[1] = sum.y, dst[2] = sum.z;
-        have_item = false;
-      }
-      if (!have_item) {
-        for (;;) {
-          unsigned item = atomicAdd(&job.counters->next_item, 1u);
-          if (item >= n_items)
-            break;
-          unsigned c = item / (tiles * 32u), pix = item - c * (tiles * 32u);
-          item_to_pixel(pix, w, h, pi, pj);
-          if (pi >= w || pj >= h)
-            continue; /* padding of the last tile column / row */
-          chunk_id = (int)c;
-          s = job.sample_begin + (int)c * plan.chunk;
-          s_end = min(s + plan.chunk, job.sample_begin + job.sample_count);
-          sum = v3(0, 0, 0);
-          pixel = v_add(v_add(px00, v_scale(du, (float)pi)), v_scale(dv, (float)pj));
-          if (job.rng_mode == RT_RNG_PIXEL)
-            rng_seed_pixel(rng, pi, pj);
-          have_item = true;
-          break;
-        }
-        if (!have_item)
-          done = true;
-      }
-      if (!done) { /* camera ray of sample s (raytracing.c:100-122) */
-        if (job.rng_mode == RT_RNG_SAMPLE)
-          rng_seed_sample(rng, pi, pj, s);
-        float jx = rng_between(rng, -0.5f, 0.5f);
-        float jy = rng_between(rng, -0.5f, 0.5f);
-        ray.o = eye;
-        if (cam.dof_angle > 0.0f) {
-          float a, b;
-          for (;;) {
-            a = rng_between(rng, -1.0f, 1.0f);
-            b = rng_between(rng, -1.0f, 1.0f);
-            if (a * a + b * b < 1.0f)
-              break;
-          }
-          ray.o = v_add(v_add(eye, v_scale(lens_u, a)), v_scale(lens_v, b));
-        }
-        ray.d = v_add(v_add(v_add(pixel, v_scale(du, jx)), v_scale(dv, jy)), v_neg(ray.o));
-        beta = v3(1, 1, 1);
-        L = v3(0, 0, 0);
-        depth = 0;
-        alive = max_depth > 0;
-        n_samples++;
-        if (!alive)
-          s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
-      }
-    }
-    /* warp-uniform exit, and the point where all 32 lanes meet again before the traversal */
-    if (__all_sync(0xffffffffu, done))
-      break;
-
-    /* ---- phase 2: one closest-hit query for every live lane, entered together */
-    TraceHit th;
-    th.t = RTC_INF, th.prim = PRIM_NONE, th.inst = RT_NONE;
-    if (alive) {
-      n_segments++;
-      th = trace_world<false, TRAV>(sc, ray, 1e-3f, RTC_INF, rng);
-    }
-    __syncwarp();
-
-    /* ---- phase 3: shade */
-    if (alive) {
-      bool ended = false;
-      if (th.prim == PRIM_NONE) {
-        L = v_add(L, v_mul(beta, background));
-        ended = true;
-      } else {
-        Hit rec;
-        trace_finalize<false>(sc, ray, th, rec);
-        V3 r_out, albedo;
-        bool skip_pdf;
-        const uint32_t tag = __ldg(&sc.materials[rec.material].tag);
-        if (tag == RT_MAT_DIFFUSE_LIGHT || tag == RT_MAT_SURFACE_NORMAL) {
-          L = v_add(L, v_mul(beta, material_emit<false>(sc, rec)));
-          ended = true;
-        } else if (!material_scatter<false>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng)) {
-          ended = true;
-        } else {
-          if (!skip_pdf && use_lights) { /* Book-3 mixture (raytracing.c:60-71) */
-            if (rng_f32(rng) < prob)
-              r_out = lights_rand<false>(sc, sc.lights_root, rec.p, rng);
-            float scatter_pdf = material_scatter_pdf(sc, rec.material, rec.n, r_out);
-            n_pdf++;
-            float sampling_pdf =
-                (1.0f - prob) * scatter_pdf + prob * lights_pdf<false>(sc, sc.lights_root, rec.p, r_out);
-            albedo = v_scale(albedo, f_div(scatter_pdf, sampling_pdf));
-          }
-          beta = v_mul(beta, albedo);
-          ray.o = rec.p;
-          ray.d = r_out;
-          depth++;
-          ended = depth >= max_depth; /* the next call would return 0 (raytracing.c:40-41) */
-        }
-      }
-      if (ended) {
-        alive = false;
-        s++;
-        if (has_nan3(L)) {
-          n_nan++;
-          if (!(job.flags & RT_FLAG_DROP_NAN))
-            sum = v_add(sum, L);
-        } else {
-          sum = v_add(sum, L);
-        }
-      }
-    }
+    unsigned item = atomicAdd(&job.counters->next_item, 1u);
+    if (item >= f.n_items)
+      return false;
+    unsigned c = item / (f.tiles * 32u), pix = item - c * (f.tiles * 32u);
+    item_to_pixel(pix, f.w, f.h, pi, pj);
+    if (pi >= f.w || pj >= f.h)
+      continue; /* padding of the last tile column / row */
+    chunk_id = (int)c;
+    return true;
   }
-  /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
+}
 
+/* camera ray of one sample (raytracing.c:100-122) */
+RTC_DEV Ray camera_ray(const Frame &f, int pi, int pj, Rng &rng) {
+  const V3 pixel = v_add(v_add(f.px00, v_scale(f.du, (float)pi)), v_scale(f.dv, (float)pj));
+  float jx = rng_between(rng, -0.5f, 0.5f);
+  float jy = rng_between(rng, -0.5f, 0.5f);
+  Ray ray;
+  ray.o = f.eye;
+  if (f.dof_angle > 0.0f) {
+    float a, b;
+    for (;;) {
+      a = rng_between(rng, -1.0f, 1.0f);
+      b = rng_between(rng, -1.0f, 1.0f);
+      if (a * a + b * b < 1.0f)
+        break;
+    }
+    ray.o = v_add(v_add(f.eye, v_scale(f.lens_u, a)), v_scale(f.lens_v, b));
+  }
+  ray.d = v_add(v_add(v_add(pixel, v_scale(f.du, jx)), v_scale(f.dv, jy)), v_neg(ray.o));
+  return ray;
+}
+
+/* One step of Camera_ray_color (raytracing.c:39-72) for a path whose closest hit is `th`: adds what the hit emits,
+ * scatters, updates the throughput.  Returns true when the path ended (its radiance L is final). */
+RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th, Ray &ray, V3 &beta, V3 &L, int &depth,
+                           Rng &rng, unsigned long long &n_pdf) {
+  if (th.prim == PRIM_NONE) {
+    L = v_add(L, v_mul(beta, f.background));
+    return true;
+  }
+  Hit rec;
+  trace_finalize<false>(sc, ray, th, rec);
+  V3 r_out, albedo;
+  bool skip_pdf;
+  const uint32_t tag = __ldg(&sc.materials[rec.material].tag);
+  if (tag == RT_MAT_DIFFUSE_LIGHT || tag == RT_MAT_SURFACE_NORMAL) {
+    L = v_add(L, v_mul(beta, material_emit<false>(sc, rec)));
+    return true;
+  }
+  if (!material_scatter<false>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng))
+    return true;
+  if (!skip_pdf && f.use_lights) { /* Book-3 mixture (raytracing.c:60-71) */
+    if (rng_f32(rng) < f.prob)
+      r_out = lights_rand<false>(sc, sc.lights_root, rec.p, rng);
+    float scatter_pdf = material_scatter_pdf(sc, rec.material, rec.n, r_out);
+    n_pdf++;
+    float sampling_pdf = (1.0f - f.prob) * scatter_pdf + f.prob * lights_pdf<false>(sc, sc.lights_root, rec.p, r_out);
+    albedo = v_scale(albedo, f_div(scatter_pdf, sampling_pdf));
+  }
+  beta = v_mul(beta, albedo);
+  ray.o = rec.p;
+  ray.d = r_out;
+  depth++;
+  return depth >= f.max_depth; /* the next call would return 0 (raytracing.c:40-41) */
+}
+
+/* warp-reduces the four counters of a render and adds them to the job's */
+RTC_DEV void flush_counters(const RenderJob &job, unsigned long long n_segments, unsigned long long n_pdf,
+                            unsigned long long n_samples, unsigned long long n_nan) {
   unsigned long long v[4] = {n_segments, n_pdf, n_samples, n_nan};
   __syncwarp();
 #pragma unroll
@@ -191,6 +149,298 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
   }
 }
 
+/* ------------------------------------------------------------------ one path per lane -------------------- */
+
+/* MINB = resident CTAs per SM the register allocation must allow (occupancy vs spills; chosen from measurements,
+ * RT_MEGA_MINB overrides for tuning) */
+template <int MINB>
+__global__ void __launch_bounds__(MEGA_BLOCK, MINB)
+    mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
+  const Frame f = frame_of(sc, job, plan);
+  unsigned long long n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+
+  /* per-lane path state */
+  Rng rng;
+  rng.state = 0, rng.inc = 1;
+  Ray ray;
+  ray.o = ray.d = v3(0, 0, 0);
+  V3 beta = v3(1, 1, 1), L = v3(0, 0, 0), sum = v3(0, 0, 0);
+  int pi = 0, pj = 0, s = 0, s_end = 0, depth = 0, chunk_id = 0;
+  bool have_item = false, alive = false;
+
+  bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
+  for (;;) {
+    /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
+    if (!alive && !done) {
+      if (have_item && s == s_end) { /* chunk finished: one store per item */
+        float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
+                     ((size_t)pj * f.w + pi) * 3;
+        dst[0] = sum.x, dst[1] = sum.y, dst[2] = sum.z;
+        have_item = false;
+      }
+      if (!have_item) {
+        if (fetch_item(f, job, pi, pj, chunk_id)) {
+          s = job.sample_begin + chunk_id * plan.chunk;
+          s_end = min(s + plan.chunk, job.sample_begin + job.sample_count);
+          sum = v3(0, 0, 0);
+          if (job.rng_mode == RT_RNG_PIXEL)
+            rng_seed_pixel(rng, pi, pj);
+          have_item = true;
+        } else {
+          done = true;
+        }
+      }
+      if (!done) {
+        if (job.rng_mode == RT_RNG_SAMPLE)
+          rng_seed_sample(rng, pi, pj, s);
+        ray = camera_ray(f, pi, pj, rng);
+        beta = v3(1, 1, 1);
+        L = v3(0, 0, 0);
+        depth = 0;
+        alive = f.max_depth > 0;
+        n_samples++;
+        if (!alive)
+          s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
+      }
+    }
+    /* warp-uniform exit, and the point where all 32 lanes meet again before the traversal */
+    if (__all_sync(0xffffffffu, done))
+      break;
+
+    /* ---- phase 2: one closest-hit query for every live lane, entered together */
+    TraceHit th;
+    {
+      uint32_t stack[TRACE_STACK];
+      Walker wk;
+      wk.stack = stack;
+      wk.begin(alive ? sc.world_root : REF_EMPTY, ray, RTC_INF);
+      auto outer = [&]() { return ray; };
+      while (__any_sync(0xffffffffu, !wk.done()))
+        walk_round_sync<true>(sc, wk, 1e-3f, outer, plan.thr8);
+      th = wk.best;
+    }
+    if (alive) {
+      n_segments++;
+      if (sc.n_media)
+        trace_media<false>(sc, ray, 1e-3f, th, rng);
+    }
+    __syncwarp();
+
+    /* ---- phase 3: shade */
+    if (alive && shade_segment(sc, f, th, ray, beta, L, depth, rng, n_pdf)) {
+      alive = false;
+      s++;
+      if (has_nan3(L)) {
+        n_nan++;
+        if (!(job.flags & RT_FLAG_DROP_NAN))
+          sum = v_add(sum, L);
+      } else {
+        sum = v_add(sum, L);
+      }
+    }
+  }
+  /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
+  flush_counters(job, n_segments, n_pdf, n_samples, n_nan);
+}
+
+/* ------------------------------------------------------------------ NV paths per lane, warp ray queue ----- */
+
+/* Path state of one "virtual lane" v = k*32 + lane (k < NV), one 32-bit word per field, laid out [field][k][lane] in
+ * the warp's slice of shared memory: a lane working on its own paths touches its own bank.  The radiance of a path
+ * needs no slot: it stays 0 until the step that ends the path (emission or background). */
+enum {
+  F_OX, F_OY, F_OZ, F_DX, F_DY, F_DZ, /* ray of the next / current segment */
+  F_BX, F_BY, F_BZ,                   /* throughput */
+  F_SX, F_SY, F_SZ,                   /* sum over the samples of the work item so far */
+  F_RNG_LO, F_RNG_HI,                 /* pcg32 state; its increment follows from the pixel column (pcg32.c:14) */
+  F_PIX,                              /* pixel: column | row << 16 */
+  F_S,                                /* sample index */
+  F_META,                             /* depth | chunk << 16 | flags */
+  F_T, F_PRIM, F_INST,                /* closest hit of the current segment, written by the warp's traversal */
+  F_COUNT
+};
+#define META_ALIVE (1u << 24)
+#define META_ITEM (1u << 25)
+#define META_DONE (1u << 26)
+
+extern __shared__ __align__(16) uint32_t mega_smem[];
+template <int NV> struct WarpSlots {
+  unsigned base; /* word offset of the warp's [F_COUNT][NV][32] words (an offset, not a pointer: the accesses stay
+                    plain shared-memory loads and stores) */
+  RTC_DEV uint32_t &u(int field, int v) const { return mega_smem[base + field * NV * 32 + v]; }
+  RTC_DEV float &f(int field, int v) const { return reinterpret_cast<float *>(mega_smem)[base + field * NV * 32 + v]; }
+  RTC_DEV V3 v3f(int field, int v) const { return v3(f(field, v), f(field + 1, v), f(field + 2, v)); }
+  RTC_DEV void put(int field, int v, V3 a) const { f(field, v) = a.x, f(field + 1, v) = a.y, f(field + 2, v) = a.z; }
+};
+template <int NV> constexpr size_t mega_queue_smem() {
+  return (size_t)(MEGA_BLOCK / 32) * ((size_t)F_COUNT * NV * 32 * 4 + (size_t)NV * 32);
+}
+RTC_DEV uint64_t rng_inc_of_column(int pi) { return ((23u + (uint64_t)pi) << 1u) | 1u; }
+
+template <int MINB, int NV>
+__global__ void __launch_bounds__(MEGA_BLOCK, MINB)
+    mega_queue_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
+  const Frame f = frame_of(sc, job, plan);
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt_mask = (1u << lane) - 1u;
+  WarpSlots<NV> S;
+  S.base = warp * F_COUNT * NV * 32;
+  const unsigned list_base = (MEGA_BLOCK / 32) * F_COUNT * NV * 32 * 4 + warp * NV * 32; /* byte offset */
+  uint8_t *const smem_bytes = reinterpret_cast<uint8_t *>(mega_smem);
+  unsigned long long n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+  const int s_last = job.sample_begin + job.sample_count;
+
+#pragma unroll
+  for (int k = 0; k < NV; k++)
+    S.u(F_META, k * 32 + lane) = 0u;
+
+  for (;;) {
+    /* ---- phase 1: regenerate the paths that ended; queue the live ones */
+    int n_list = 0;
+    bool all_done = true;
+#pragma unroll 1
+    for (int k = 0; k < NV; k++) {
+      const int v = k * 32 + (int)lane;
+      uint32_t meta = S.u(F_META, v);
+      if (!(meta & (META_ALIVE | META_DONE))) {
+        uint32_t pix = S.u(F_PIX, v);
+        int pi = (int)(pix & 0xffffu), pj = (int)(pix >> 16), s = (int)S.u(F_S, v), chunk_id = (int)((meta >> 16) & 0xffu);
+        if (meta & META_ITEM) {
+          const int s_end = min(job.sample_begin + (chunk_id + 1) * plan.chunk, s_last);
+          if (s == s_end) { /* chunk finished: one store per item */
+            float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
+                         ((size_t)pj * f.w + pi) * 3;
+            dst[0] = S.f(F_SX, v), dst[1] = S.f(F_SY, v), dst[2] = S.f(F_SZ, v);
+            meta &= ~META_ITEM;
+          }
+        }
+        Rng rng;
+        bool seeded = false;
+        if (!(meta & META_ITEM)) {
+          if (fetch_item(f, job, pi, pj, chunk_id)) {
+            s = job.sample_begin + chunk_id * plan.chunk;
+            S.put(F_SX, v, v3(0, 0, 0));
+            S.u(F_PIX, v) = (uint32_t)pi | ((uint32_t)pj << 16);
+            if (job.rng_mode == RT_RNG_PIXEL) {
+              rng_seed_pixel(rng, pi, pj);
+              seeded = true;
+            }
+            meta = META_ITEM | ((uint32_t)chunk_id << 16);
+          } else {
+            meta = META_DONE;
+          }
+        }
+        if (!(meta & META_DONE)) {
+          if (job.rng_mode == RT_RNG_SAMPLE) {
+            rng_seed_sample(rng, pi, pj, s);
+          } else if (!seeded) {
+            rng.state = (uint64_t)S.u(F_RNG_LO, v) | ((uint64_t)S.u(F_RNG_HI, v) << 32);
+            rng.inc = rng_inc_of_column(pi);
+          }
+          const Ray ray = camera_ray(f, pi, pj, rng);
+          S.put(F_OX, v, ray.o);
+          S.put(F_DX, v, ray.d);
+          S.put(F_BX, v, v3(1, 1, 1));
+          S.u(F_RNG_LO, v) = (uint32_t)rng.state, S.u(F_RNG_HI, v) = (uint32_t)(rng.state >> 32);
+          meta &= ~0xffffu; /* depth 0 */
+          n_samples++;
+          if (f.max_depth > 0)
+            meta |= META_ALIVE;
+          else
+            s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
+          S.u(F_S, v) = (uint32_t)s;
+        }
+        S.u(F_META, v) = meta;
+      }
+      const bool alive = (meta & META_ALIVE) != 0u;
+      const unsigned m = __ballot_sync(0xffffffffu, alive);
+      if (alive) {
+        smem_bytes[list_base + n_list + __popc(m & lt_mask)] = (uint8_t)v;
+        n_segments++;
+      }
+      n_list += __popc(m);
+      all_done = all_done && __all_sync(0xffffffffu, (meta & META_DONE) != 0u);
+    }
+    if (all_done)
+      break;
+    __syncwarp();
+
+    /* ---- phase 2: the warp's n_list rays, handed to its lanes as they become free */
+    {
+      uint32_t stack[TRACE_STACK];
+      Walker wk;
+      wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 0;
+      int mine = -1, next = 0;
+      auto outer = [&]() { /* the ray as queued (only needed again when the walk leaves an instance) */
+        Ray q;
+        q.o = S.v3f(F_OX, mine), q.d = S.v3f(F_DX, mine);
+        return q;
+      };
+      for (;;) {
+        const bool idle = wk.done();
+        const unsigned m = __ballot_sync(0xffffffffu, idle);
+        if (m != 0u) { /* some lane finished its ray (or has none yet): park the hit, take the next ray */
+          if (idle && mine >= 0) {
+            S.f(F_T, mine) = wk.best.t, S.u(F_PRIM, mine) = wk.best.prim, S.u(F_INST, mine) = wk.best.inst;
+            mine = -1;
+          }
+          if (next < n_list) {
+            const int idx = next + __popc(m & lt_mask);
+            if (idle && idx < n_list) {
+              mine = smem_bytes[list_base + idx];
+              wk.begin(sc.world_root, outer(), RTC_INF);
+            }
+            next += __popc(m);
+          } else if (m == 0xffffffffu) {
+            break;
+          }
+        }
+        walk_round_sync<true>(sc, wk, 1e-3f, outer, plan.thr8);
+      }
+    }
+    __syncwarp();
+
+    /* ---- phase 3: shade */
+#pragma unroll 1
+    for (int k = 0; k < NV; k++) {
+      const int v = k * 32 + (int)lane;
+      uint32_t meta = S.u(F_META, v);
+      if (meta & META_ALIVE) {
+        Ray ray;
+        ray.o = S.v3f(F_OX, v), ray.d = S.v3f(F_DX, v);
+        TraceHit th;
+        th.t = S.f(F_T, v), th.prim = S.u(F_PRIM, v), th.inst = S.u(F_INST, v);
+        Rng rng;
+        rng.state = (uint64_t)S.u(F_RNG_LO, v) | ((uint64_t)S.u(F_RNG_HI, v) << 32);
+        rng.inc = rng_inc_of_column((int)(S.u(F_PIX, v) & 0xffffu));
+        V3 beta = S.v3f(F_BX, v), L = v3(0, 0, 0);
+        int depth = (int)(meta & 0xffffu);
+        if (sc.n_media)
+          trace_media<false>(sc, ray, 1e-3f, th, rng);
+        if (shade_segment(sc, f, th, ray, beta, L, depth, rng, n_pdf)) {
+          meta &= ~META_ALIVE;
+          S.u(F_S, v) += 1u;
+          bool add = true;
+          if (has_nan3(L)) {
+            n_nan++;
+            add = !(job.flags & RT_FLAG_DROP_NAN);
+          }
+          if (add)
+            S.put(F_SX, v, v_add(S.v3f(F_SX, v), L));
+        } else {
+          S.put(F_OX, v, ray.o);
+          S.put(F_DX, v, ray.d);
+          S.put(F_BX, v, beta);
+          meta = (meta & ~0xffffu) | (uint32_t)depth;
+        }
+        S.u(F_RNG_LO, v) = (uint32_t)rng.state, S.u(F_RNG_HI, v) = (uint32_t)(rng.state >> 32);
+        S.u(F_META, v) = meta;
+      }
+    }
+    __syncwarp();
+  }
+  flush_counters(job, n_segments, n_pdf, n_samples, n_nan);
+}
+
 /* radiance[p] = sum over chunks, in chunk order (deterministic) */
 __global__ void mega_sum_chunks_kernel(const float *__restrict__ partial, float *__restrict__ radiance, size_t n_values,
                                        int n_chunks) {
@@ -203,28 +453,46 @@ __global__ void mega_sum_chunks_kernel(const float *__restrict__ partial, float 
   radiance[i] = acc;
 }
 
+/* ------------------------------------------------------------------ launch ------------------------------- */
+
 typedef void (*MegaKernel)(const DScene, const RenderJob, const MegaPlan, float *);
-static MegaKernel mega_kernel_for(int minb, int trav) {
-  if (trav == 1)
-    return minb == 4 ? mega_render_kernel<4, 1> : minb == 6 ? mega_render_kernel<6, 1> : mega_render_kernel<8, 1>;
-  return minb == 4 ? mega_render_kernel<4, 0> : minb == 6 ? mega_render_kernel<6, 0> : mega_render_kernel<8, 0>;
+struct MegaVariant {
+  int nv, minb; /* nv = 0: one path per lane (registers) */
+  MegaKernel fn;
+  size_t smem;
+};
+static const MegaVariant mega_variants[] = {
+    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>()}, /* first entry of an nv = its default */
+    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>()},
+    {0, 8, mega_render_kernel<8>, 0},
+    {0, 6, mega_render_kernel<6>, 0},
+    {0, 4, mega_render_kernel<4>, 0},
+};
+static int env_int(const char *name, int fallback) {
+  const char *v = getenv(name);
+  return v ? atoi(v) : fallback;
 }
-static int mega_trav() { /* 0 = while-while, 1 = leaves intersected inside the node loop */
-  static int cached = -1;
-  if (cached < 0) {
-    const char *v = getenv("RT_MEGA_TRAV");
-    cached = v ? (atoi(v) == 1 ? 1 : 0) : 0;
+/* RT_MEGA_NV (paths per lane, 0 = the register kernel) and RT_MEGA_MINB (CTAs per SM the registers must allow) pick
+ * the variant; a combination that is not built falls back to the nv's default minb, then to the default variant. */
+static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks) {
+  static int nv = -1, minb = -1;
+  if (nv < 0) {
+    nv = env_int("RT_MEGA_NV", MEGA_NV_DEFAULT);
+    minb = env_int("RT_MEGA_MINB", 0);
   }
-  return cached;
-}
-static int mega_minb() {
-  static int cached = 0;
-  if (cached == 0) {
-    const char *v = getenv("RT_MEGA_MINB");
-    int m = v ? atoi(v) : 8;
-    cached = (m == 4 || m == 6 || m == 8) ? m : 8;
-  }
-  return cached;
+  int want_nv = nv;
+  /* the slot layout packs the pixel into 16+16 bits, the depth into 16 and the chunk into 8 */
+  if (cam.img_width > 65535 || cam.img_height > 65535 || cam.max_depth > 65535 || n_chunks > 256)
+    want_nv = 0;
+  const int n = (int)(sizeof(mega_variants) / sizeof(mega_variants[0]));
+  for (int pass = 0; pass < 2; pass++)
+    for (int i = 0; i < n; i++)
+      if (mega_variants[i].nv == want_nv && (pass == 1 || mega_variants[i].minb == minb))
+        return &mega_variants[i];
+  for (int i = 0; i < n; i++)
+    if (mega_variants[i].nv == 0)
+      return &mega_variants[i];
+  return &mega_variants[0];
 }
 
 cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, MegaPlan *plan) {
@@ -232,41 +500,65 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   cudaError_t err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (err != cudaSuccess)
     return err;
-  plan->minb = mega_minb();
-  plan->trav = mega_trav();
-  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mega_kernel_for(plan->minb, plan->trav), MEGA_BLOCK, 0);
+  /* chunking first (the variant depends on it only through a capacity check); the grid size is needed for the
+   * chunk count, so take the default variant's occupancy for that estimate */
+  const MegaVariant *var = mega_variant(cam, 1);
+  if (var->smem > 48 * 1024) {
+    err = cudaFuncSetAttribute(var->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)var->smem);
+    if (err != cudaSuccess)
+      return err;
+  }
+  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, MEGA_BLOCK, var->smem);
   if (err != cudaSuccess)
     return err;
   if (per_sm < 1)
     per_sm = 1;
   plan->blocks = sms * per_sm;
   plan->threads = MEGA_BLOCK;
-  const long long lanes = (long long)plan->blocks * MEGA_BLOCK;
+  const long long paths = (long long)plan->blocks * MEGA_BLOCK * (var->nv > 0 ? var->nv : 1);
   const long long pixels = (long long)cam.img_width * cam.img_height;
   int n_chunks = 1;
   if (rng_mode == RT_RNG_SAMPLE && pixels > 0) {
-    /* enough items that the end-of-kernel tail (lanes waiting for the last items) stays small, but chunks of at
+    /* enough items that the end-of-kernel tail (paths waiting for the last items) stays small, but chunks of at
      * least 8 samples so the per-item store and fetch are noise */
-    long long want = (64 * lanes + pixels - 1) / pixels;
+    long long want = (64 * paths + pixels - 1) / pixels;
     long long most = sample_count / 8;
     n_chunks = (int)(want < 1 ? 1 : want);
     if (n_chunks > most)
       n_chunks = (int)(most < 1 ? 1 : most);
     if (n_chunks > 64)
       n_chunks = 64;
-    const char *env = getenv("RT_MEGA_CHUNKS"); /* tuning */
-    if (env && atoi(env) > 0 && atoi(env) <= sample_count)
-      n_chunks = atoi(env);
+    int env = env_int("RT_MEGA_CHUNKS", 0); /* tuning */
+    if (env > 0 && env <= sample_count)
+      n_chunks = env;
   }
   plan->chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->n_chunks = plan->chunk > 0 ? (sample_count + plan->chunk - 1) / plan->chunk : 1;
   plan->partial_bytes = plan->n_chunks > 1 ? (size_t)plan->n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
+  if (mega_variant(cam, plan->n_chunks) != var) { /* capacity check failed: the register kernel, its own grid */
+    var = mega_variant(cam, plan->n_chunks);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, MEGA_BLOCK, var->smem);
+    if (err != cudaSuccess)
+      return err;
+    plan->blocks = sms * (per_sm < 1 ? 1 : per_sm);
+  }
+  plan->variant = (int)(var - mega_variants);
+  {
+    int t = env_int("RT_MEGA_THR8", MEGA_THR8_DEFAULT); /* see walk_round_sync */
+    plan->thr8 = t < 0 ? 0 : t > 8 ? 8 : t;
+  }
+  plan->nv = var->nv;
+  plan->minb = var->minb;
   return cudaSuccess;
 }
 
 cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
                         cudaStream_t stream, int *launches) {
-  mega_kernel_for(plan.minb, plan.trav)<<<plan.blocks, plan.threads, 0, stream>>>(sc, job, plan, partial);
+  *launches = 0;
+  if (plan.variant < 0 || plan.variant >= (int)(sizeof(mega_variants) / sizeof(mega_variants[0])))
+    return cudaErrorInvalidValue;
+  const MegaVariant *var = &mega_variants[plan.variant];
+  var->fn<<<plan.blocks, plan.threads, var->smem, stream>>>(sc, job, plan, partial);
   cudaError_t err = cudaGetLastError();
   *launches = 1;
   if (err != cudaSuccess)
@@ -283,7 +575,7 @@ cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &
 
 /* ------------------------------------------------------------------ rt_hit_batch over the rebuilt BVH ---- */
 
-template <int TRAV> __global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kernel(const DScene sc, const HitBatch b) {
+__global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kernel(const DScene sc, const HitBatch b) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= b.n)
     return;
@@ -295,7 +587,7 @@ template <int TRAV> __global__ void __launch_bounds__(MEGA_BLOCK) mega_hit_kerne
     g.state = b.rng_io[2 * i];
     g.inc = b.rng_io[2 * i + 1];
   }
-  TraceHit th = trace_world<true, TRAV>(sc, ray, b.t_min, b.t_max, g);
+  TraceHit th = trace_world<true>(sc, ray, b.t_min, b.t_max, g);
   if (b.rng_io)
     b.rng_io[2 * i] = g.state;
   const bool hit = th.prim != PRIM_NONE;
@@ -322,9 +614,6 @@ cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t str
   if (b.n == 0)
     return cudaSuccess;
   unsigned blocks = (unsigned)((b.n + MEGA_BLOCK - 1) / MEGA_BLOCK);
-  if (mega_trav() == 1)
-    mega_hit_kernel<1><<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
-  else
-    mega_hit_kernel<0><<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
+  mega_hit_kernel<<<blocks, MEGA_BLOCK, 0, stream>>>(sc, b);
   return cudaGetLastError();
 }

@@ -24,8 +24,8 @@
 #define REF_INDEX(r) ((r)&0x1FFFFFFu)
 #define MAKE_REF(kind, count, index) (((uint32_t)(kind) << 30) | (((uint32_t)(count)-1u) << 25) | (uint32_t)(index))
 
-/* binary node holding BOTH children's boxes: four 16-byte loads per visit */
-struct __align__(16) BNode {
+/* binary node holding BOTH children's boxes: two 32-byte loads per visit */
+struct __align__(32) BNode {
   float4 xy0; /* child0: x.lo x.hi y.lo y.hi */
   float4 xy1; /* child1: x.lo x.hi y.lo y.hi */
   float4 zz;  /* child0 z.lo z.hi, child1 z.lo z.hi */

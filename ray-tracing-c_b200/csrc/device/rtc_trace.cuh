@@ -14,6 +14,17 @@
 
 #include "rtc_shade.cuh"
 
+/* tuning switches of the node loop (defaults = what measured best on B200) */
+#ifndef RTC_NODE_WIDE
+#define RTC_NODE_WIDE 1 /* 256-bit node loads in the render kernels' inlined loops */
+#endif
+#ifndef RTC_VISITS_PER_VOTE
+#define RTC_VISITS_PER_VOTE 1
+#endif
+#ifndef RTC_SLAB_ONE_FMA
+#define RTC_SLAB_ONE_FMA 1
+#endif
+
 #define TRACE_STACK 48          /* rt_scene_create refuses deeper structures for the mega/wave kernels */
 #define TRACE_SENTINEL 0xFFFFFFFEu
 #define PRIM_NONE 0xFFFFFFFFu
@@ -49,6 +60,28 @@ RTC_DEV void chain_unapply(const DScene &sc, uint32_t op_begin, uint32_t op_coun
   }
 }
 
+/* One 64-byte BNode.  WIDE: two 256-bit read-only loads (LDG.E.256, sm_100+) instead of four 128/64-bit ones --
+ * half the load instructions and half the L1 wavefronts of the node loop.  Only the kernels' own inlined node loops
+ * use it: ptxas 12.9 crashes on a 256-bit load inside a device FUNCTION that two kernels of a module call
+ * (trace_group_call), so the out-of-line walks keep the 128-bit loads. */
+template <bool WIDE> RTC_DEV void ldg_node(const BNode *n, float4 &xy0, float4 &xy1, float4 &zz, uint2 &ch) {
+  if (WIDE) {
+    uint32_t a0, a1, a2, a3, a4, a5, a6, a7, b0, b1, b2, b3, pad0, pad1;
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3), "=r"(a4), "=r"(a5), "=r"(a6), "=r"(a7)
+        : "l"(n));
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3), "=r"(ch.x), "=r"(ch.y), "=r"(pad0), "=r"(pad1)
+        : "l"(reinterpret_cast<const char *>(n) + 32));
+    xy0 = make_float4(__uint_as_float(a0), __uint_as_float(a1), __uint_as_float(a2), __uint_as_float(a3));
+    xy1 = make_float4(__uint_as_float(a4), __uint_as_float(a5), __uint_as_float(a6), __uint_as_float(a7));
+    zz = make_float4(__uint_as_float(b0), __uint_as_float(b1), __uint_as_float(b2), __uint_as_float(b3));
+  } else {
+    xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
+    ch = __ldg(reinterpret_cast<const uint2 *>(&n->child0));
+  }
+}
+
 struct TraceHit {
   float t;
   uint32_t prim; /* PRIM_NONE, or kind/index reference into msph / mquads / media */
@@ -78,17 +111,21 @@ RTC_DEV SlabRay slab_setup(const Ray &r) {
   return s;
 }
 
-/* Entry distance of the ray into the box, or +inf if it misses [t_min, t_max].  NaNs (0 * inf on an axis the ray
- * is parallel to) are dropped by fminf/fmaxf, which errs on the side of visiting. */
-RTC_DEV float slab_entry(const SlabRay &s, float xlo, float xhi, float ylo, float yhi, float zlo, float zhi,
-                         float t_min, float t_max) {
+/* Does the ray meet the box within [t_min, t_max]?  `enter` = its entry distance (for ordering the children).  NaNs
+ * (0 * inf on an axis the ray is parallel to) are dropped by fminf/fmaxf, which errs on the side of visiting; the
+ * exit distance carries a relative + an absolute slack so that a true hit is never culled. */
+template <bool NONNEG>
+RTC_DEV bool slab_test(const SlabRay &s, float xlo, float xhi, float ylo, float yhi, float zlo, float zhi, float t_min,
+                       float t_max, float &enter) {
   float x0 = fmaf(xlo, s.inv.x, -s.oi.x), x1 = fmaf(xhi, s.inv.x, -s.oi.x);
   float y0 = fmaf(ylo, s.inv.y, -s.oi.y), y1 = fmaf(yhi, s.inv.y, -s.oi.y);
   float z0 = fmaf(zlo, s.inv.z, -s.oi.z), z1 = fmaf(zhi, s.inv.z, -s.oi.z);
-  float enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
+  enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
   float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
-  leave = fmaf(fabsf(leave), 4e-7f, leave) + s.slack; /* relative + absolute slack: never cull a true hit */
-  return enter <= leave ? enter : RTC_INF;
+  /* NONNEG: the caller's t_min is >= 0, so a negative exit distance is a miss whatever the slack does to it and
+   * one FMA serves (leave * (1 + 4e-7) only widens a non-negative exit) */
+  leave = (NONNEG && RTC_SLAB_ONE_FMA) ? fmaf(leave, 1.0000004f, s.slack) : fmaf(fabsf(leave), 4e-7f, leave) + s.slack;
+  return enter <= leave;
 }
 
 /* sphere_isect with t_max INCLUDED, so that the traversal can see exact ties and resolve them like the reference */
@@ -166,151 +203,124 @@ RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float 
   }
 }
 
-/* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame). */
-RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r_in, float t_min, float t_max) {
+/* State of one closest-hit query over a group.  A walker is always in one of three states: it holds an INNER node
+ * (wants a two-box visit), it holds a LEAF (a primitive range, or an instance to enter), or it is done
+ * (cur == REF_EMPTY).  The scheduling of visit() and leaf() steps across the lanes of a warp is the caller's:
+ * trace_group() below for one ray per lane, the megakernel's warp ray queue for dynamic assignment. */
+struct Walker {
+  uint32_t *stack;    /* TRACE_STACK entries owned by the caller (a separate local array, so that the scalar members
+                         below stay in registers) */
+  int sp;
+  Ray r;              /* ray in the current frame (the group's own, or an instance's) */
+  SlabRay slab;
+  uint32_t cur;       /* subtree to look at next */
+  uint32_t cur_inst;  /* instance whose frame the walk is in, RT_NONE for the group's own frame */
+  uint32_t best_node; /* node id of the best quad (only consulted on exact ties) */
   TraceHit best;
-  best.t = t_max, best.prim = PRIM_NONE, best.inst = RT_NONE;
-  if (root == REF_EMPTY)
-    return best;
 
-  uint32_t stack[TRACE_STACK];
-  int sp = 0;
-  Ray r = r_in;
-  SlabRay slab = slab_setup(r);
-  uint32_t cur = root, cur_inst = RT_NONE;
-  uint32_t best_node = 0; /* node id of the best quad (only consulted on exact ties) */
+  /* The ray in the group's own frame and t_min are not kept here: the caller passes them to every step (`outer` is
+   * a callable returning that ray -- a register copy, or a reload from wherever the caller parked it). */
+  RTC_DEV void begin(uint32_t root, const Ray &ray, float tmax) {
+    sp = 0, r = ray, slab = slab_setup(ray);
+    cur = root, cur_inst = RT_NONE, best_node = 0;
+    best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
+  }
+  RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
+  RTC_DEV bool done() const { return cur == REF_EMPTY; }
 
-  /* pops the next subtree; leaving an instance (sentinel) restores the outer ray */
-  auto pop = [&]() -> uint32_t {
+  /* next subtree from the stack; leaving an instance (sentinel) restores the outer ray */
+  template <class Outer> RTC_DEV uint32_t pop(Outer outer) {
     for (;;) {
       if (sp == 0)
         return REF_EMPTY;
-      uint32_t c = stack[--sp];
-      if (c != TRACE_SENTINEL)
-        return c;
-      r = r_in;
+      uint32_t e = stack[--sp];
+      if (e != TRACE_SENTINEL)
+        return e;
+      r = outer();
       slab = slab_setup(r);
       cur_inst = RT_NONE;
     }
-  };
-
-  /* "while-while": all lanes of a warp first walk inner nodes together until each holds a leaf (or is done), then
-   * all process leaves together -- keeps the 32 lanes in the same code far more often than one if/else per step */
-  for (;;) {
-    while (REF_KIND(cur) == REF_INNER) {
-      const BNode *n = &sc.bnodes[REF_INDEX(cur)];
-      const float4 xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
-      const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(&n->child0));
-      float e0 = slab_entry(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t);
-      float e1 = slab_entry(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t);
-      bool h0 = e0 < RTC_INF, h1 = e1 < RTC_INF;
-      if (h0 && h1) {
-        bool swap = e1 < e0;
-        stack[sp++] = swap ? ch.x : ch.y;
-        cur = swap ? ch.y : ch.x;
-      } else if (h0 || h1) {
-        cur = h0 ? ch.x : ch.y;
-      } else {
-        cur = pop();
-      }
+  }
+  /* one inner node: both children's boxes, nearer child first, the other one pushed */
+  template <bool NONNEG, class Outer> RTC_DEV void visit(const DScene &sc, float t_min, Outer outer) {
+    /* an inner reference is its node index (kind 0, count field 0): no masking, one multiply-add for the address;
+     * the 64-byte node arrives in two 256-bit loads */
+    float4 xy0, xy1, zz;
+    uint2 ch;
+    ldg_node<NONNEG && RTC_NODE_WIDE>(sc.bnodes + cur, xy0, xy1, zz, ch); /* NONNEG = the render kernels' inlined loops */
+    float e0, e1;
+    const bool h0 = slab_test<NONNEG>(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t, e0);
+    const bool h1 = slab_test<NONNEG>(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t, e1);
+    if (h0 && h1) {
+      const bool swap = e1 < e0;
+      stack[sp++] = swap ? ch.x : ch.y;
+      cur = swap ? ch.y : ch.x;
+    } else if (h0 || h1) {
+      cur = h0 ? ch.x : ch.y;
+    } else {
+      cur = pop(outer);
     }
-    if (cur == REF_EMPTY)
-      break;
+  }
+  /* one leaf reference: primitives, or an instance whose frame is entered (a sentinel brings the outer ray back) */
+  template <class Outer> RTC_DEV void leaf(const DScene &sc, float t_min, Outer outer) {
     if (REF_KIND(cur) != REF_INSTANCE) {
       leaf_intersect(sc, cur, r, t_min, cur_inst, best, best_node);
-    } else { /* instance: enter its frame; a sentinel on the stack brings the outer ray back */
+    } else {
       const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
       if (inst.z != REF_EMPTY) {
         stack[sp++] = TRACE_SENTINEL;
         cur_inst = REF_INDEX(cur);
-        r = chain_apply(sc, inst.x, inst.y, r_in);
+        r = chain_apply(sc, inst.x, inst.y, outer());
         slab = slab_setup(r);
         cur = inst.z;
-        continue;
+        return;
       }
     }
-    cur = pop();
+    cur = pop(outer);
   }
-  return best;
+};
+
+/* One round of a WARP-SYNCHRONOUS walk (all 32 lanes call it together, a lane without a ray with w.done()):
+ * descend while at least `thr8` eighths of the warp's busy lanes hold an inner node, then the lanes that hold a leaf
+ * process it.  thr8 = 0 is the classic "while-while" (descend while ANY lane holds an inner node): there one lane on
+ * a long descent keeps every lane that already has its leaf waiting -- ncu on Book 1: descents are geometric with
+ * mean 3.5 visits, the longest of 32 is 10.7, so 10.6 of 32 lanes are active in the node loop.  Leaving the loop
+ * early costs nothing: a lane that is still descending just carries on in the next round. */
+template <bool NONNEG, class Outer>
+RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer outer, int thr8) {
+  const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
+  const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
+  for (;;) {
+    const bool in = w.at_inner();
+    if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
+      break;
+    if (in) { /* two visits per vote: halves the cost of voting */
+      w.visit<NONNEG>(sc, t_min, outer);
+      if (RTC_VISITS_PER_VOTE > 1 && w.at_inner())
+        w.visit<NONNEG>(sc, t_min, outer);
+    }
+  }
+  if (!w.at_inner() && !w.done())
+    w.leaf(sc, t_min, outer);
 }
 
-/* Variant: primitive leaves are intersected INSIDE the node loop, the moment their box is hit, so a lane never waits
- * for the rest of its warp to reach a leaf; the stack holds inner nodes (and instances) only.  Same results. */
-RTC_DEV TraceHit trace_group_inline(const DScene &sc, uint32_t root, const Ray &r_in, float t_min, float t_max) {
-  TraceHit best;
-  best.t = t_max, best.prim = PRIM_NONE, best.inst = RT_NONE;
-  if (root == REF_EMPTY)
-    return best;
-
+/* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame), one ray per lane.
+ * "while-while": all lanes of a warp first descend inner nodes together until each holds a leaf (or is done), then
+ * all process leaves together -- keeps the 32 lanes in the same code far more often than one if/else per step. */
+RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r, float t_min, float t_max) {
   uint32_t stack[TRACE_STACK];
-  int sp = 0;
-  Ray r = r_in;
-  SlabRay slab = slab_setup(r);
-  uint32_t cur = root, cur_inst = RT_NONE;
-  uint32_t best_node = 0;
-
-  auto pop = [&]() -> uint32_t {
-    for (;;) {
-      if (sp == 0)
-        return REF_EMPTY;
-      uint32_t c = stack[--sp];
-      if (c != TRACE_SENTINEL)
-        return c;
-      r = r_in;
-      slab = slab_setup(r);
-      cur_inst = RT_NONE;
-    }
-  };
-
-  while (cur != REF_EMPTY) {
-    if (REF_KIND(cur) != REF_INNER) { /* only a group/instance root or a deferred instance arrives here */
-      if (REF_KIND(cur) == REF_INSTANCE) {
-        const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
-        if (inst.z != REF_EMPTY) {
-          stack[sp++] = TRACE_SENTINEL;
-          cur_inst = REF_INDEX(cur);
-          r = chain_apply(sc, inst.x, inst.y, r_in);
-          slab = slab_setup(r);
-          cur = inst.z;
-          continue;
-        }
-      } else {
-        leaf_intersect(sc, cur, r, t_min, cur_inst, best, best_node);
-      }
-      cur = pop();
-      continue;
-    }
-    const BNode *n = &sc.bnodes[REF_INDEX(cur)];
-    const float4 xy0 = __ldg(&n->xy0), xy1 = __ldg(&n->xy1), zz = __ldg(&n->zz);
-    const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(&n->child0));
-    float e0 = slab_entry(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t);
-    float e1 = slab_entry(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t);
-    const bool swap = e1 < e0;
-    uint32_t c_near = swap ? ch.y : ch.x, c_far = swap ? ch.x : ch.y;
-    float e_near = swap ? e1 : e0, e_far = swap ? e0 : e1;
-    uint32_t next = REF_EMPTY;
-#pragma unroll 1
-    for (int k = 0; k < 2; k++) { /* near child, then far child (one copy of the leaf code) */
-      const uint32_t c = k ? c_far : c_near;
-      const float e = k ? e_far : e_near;
-      if (!(e < RTC_INF) || e > best.t) /* missed, or a closer hit was found meanwhile */
-        continue;
-      const uint32_t kind = REF_KIND(c);
-      if (kind == REF_SPHERES || kind == REF_QUADS) {
-        leaf_intersect(sc, c, r, t_min, cur_inst, best, best_node);
-      } else if (next == REF_EMPTY) {
-        next = c;
-      } else {
-        stack[sp++] = c;
-      }
-    }
-    cur = next != REF_EMPTY ? next : pop();
+  Walker w;
+  w.stack = stack;
+  w.begin(root, r, t_max);
+  auto outer = [&]() { return r; };
+  for (;;) {
+    while (w.at_inner())
+      w.visit<false>(sc, t_min, outer);
+    if (w.done())
+      break;
+    w.leaf(sc, t_min, outer);
   }
-  return best;
-}
-
-template <int TRAV> RTC_DEV TraceHit trace_group_mode(const DScene &sc, uint32_t root, const Ray &r, float t_min, float t_max) {
-  return TRAV == 1 ? trace_group_inline(sc, root, r, t_min, t_max) : trace_group(sc, root, r, t_min, t_max);
+  return w.best;
 }
 
 static __device__ __noinline__ TraceHit trace_group_call(const DScene &sc, uint32_t root, const Ray &r, float t_min,
@@ -399,9 +409,8 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
 }
 
 /* The integrator's query (raytracing.c:45): surfaces, then media. */
-template <bool EXACT, int TRAV = 0>
-RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
-  TraceHit best = trace_group_mode<TRAV>(sc, sc.world_root, world, t_min, t_max);
+template <bool EXACT> RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
+  TraceHit best = trace_group(sc, sc.world_root, world, t_min, t_max);
   if (sc.n_media)
     trace_media<EXACT>(sc, world, t_min, best, g);
   return best;

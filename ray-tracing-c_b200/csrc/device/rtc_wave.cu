@@ -345,7 +345,7 @@ cudaError_t wave_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
     if (chunk_env && atoi(chunk_env) > 0 && atoi(chunk_env) <= sample_count)
       n_chunks = atoi(chunk_env);
   }
-  plan->mega.blocks = 0, plan->mega.threads = 0, plan->mega.minb = 0, plan->mega.trav = 0;
+  plan->mega.blocks = 0, plan->mega.threads = 0, plan->mega.minb = 0, plan->mega.nv = 0;
   plan->mega.chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->mega.n_chunks = (sample_count + plan->mega.chunk - 1) / plan->mega.chunk;
   plan->mega.partial_bytes =
