@@ -101,7 +101,7 @@ RTC_DEV Ray camera_ray(const Frame &f, int pi, int pj, Rng &rng) {
 /* One step of Camera_ray_color (raytracing.c:39-72) for a path whose closest hit is `th`: adds what the hit emits,
  * scatters, updates the throughput.  Returns true when the path ended (its radiance L is final). */
 RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th, Ray &ray, V3 &beta, V3 &L, int &depth,
-                           Rng &rng, unsigned long long &n_pdf) {
+                           Rng &rng, unsigned &n_pdf) {
   if (th.prim == PRIM_NONE) {
     L = v_add(L, v_mul(beta, f.background));
     return true;
@@ -133,8 +133,8 @@ RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th,
 }
 
 /* warp-reduces the four counters of a render and adds them to the job's */
-RTC_DEV void flush_counters(const RenderJob &job, unsigned long long n_segments, unsigned long long n_pdf,
-                            unsigned long long n_samples, unsigned long long n_nan) {
+RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned n_pdf, unsigned n_samples,
+                            unsigned n_nan) {
   unsigned long long v[4] = {n_segments, n_pdf, n_samples, n_nan};
   __syncwarp();
 #pragma unroll
@@ -157,22 +157,24 @@ template <int MINB>
 __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
-  unsigned long long n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+  /* per-lane counts of one launch: a lane would need days to overflow 32 bits */
+  unsigned n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
 
   /* per-lane path state */
   Rng rng;
   rng.state = 0, rng.inc = 1;
   Ray ray;
   ray.o = ray.d = v3(0, 0, 0);
-  V3 beta = v3(1, 1, 1), L = v3(0, 0, 0), sum = v3(0, 0, 0);
-  int pi = 0, pj = 0, s = 0, s_end = 0, depth = 0, chunk_id = 0;
+  V3 beta = v3(1, 1, 1), sum = v3(0, 0, 0);
+  int pi = 0, pj = 0, s = 0, depth = 0, chunk_id = 0;
   bool have_item = false, alive = false;
 
   bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
   for (;;) {
     /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
     if (!alive && !done) {
-      if (have_item && s == s_end) { /* chunk finished: one store per item */
+      if (have_item && s == min(job.sample_begin + (chunk_id + 1) * plan.chunk, job.sample_begin + job.sample_count)) {
+        /* chunk finished: one store per item */
         float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
                      ((size_t)pj * f.w + pi) * 3;
         dst[0] = sum.x, dst[1] = sum.y, dst[2] = sum.z;
@@ -181,7 +183,6 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
       if (!have_item) {
         if (fetch_item(f, job, pi, pj, chunk_id)) {
           s = job.sample_begin + chunk_id * plan.chunk;
-          s_end = min(s + plan.chunk, job.sample_begin + job.sample_count);
           sum = v3(0, 0, 0);
           if (job.rng_mode == RT_RNG_PIXEL)
             rng_seed_pixel(rng, pi, pj);
@@ -195,7 +196,6 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
           rng_seed_sample(rng, pi, pj, s);
         ray = camera_ray(f, pi, pj, rng);
         beta = v3(1, 1, 1);
-        L = v3(0, 0, 0);
         depth = 0;
         alive = f.max_depth > 0;
         n_samples++;
@@ -226,7 +226,9 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
     }
     __syncwarp();
 
-    /* ---- phase 3: shade */
+    /* ---- phase 3: shade.  The radiance of a path stays 0 until the step that ends it (emission or background),
+     * so it is not part of the state a lane carries through the walk. */
+    V3 L = v3(0, 0, 0);
     if (alive && shade_segment(sc, f, th, ray, beta, L, depth, rng, n_pdf)) {
       alive = false;
       s++;
@@ -286,7 +288,8 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
   S.base = warp * F_COUNT * NV * 32;
   const unsigned list_base = (MEGA_BLOCK / 32) * F_COUNT * NV * 32 * 4 + warp * NV * 32; /* byte offset */
   uint8_t *const smem_bytes = reinterpret_cast<uint8_t *>(mega_smem);
-  unsigned long long n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+  /* per-lane counts of one launch: a lane would need days to overflow 32 bits */
+  unsigned n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
   const int s_last = job.sample_begin + job.sample_count;
 
 #pragma unroll

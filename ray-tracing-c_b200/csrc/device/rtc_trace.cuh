@@ -21,6 +21,20 @@
 #ifndef RTC_VISITS_PER_VOTE
 #define RTC_VISITS_PER_VOTE 1
 #endif
+#ifndef RTC_CHAIN_INLINE
+#define RTC_CHAIN_INLINE 1 /* instance transforms inlined into the walk (1) or out of line (0); measured */
+#endif
+#if RTC_CHAIN_INLINE
+#define RTC_CHAIN_ATTR RTC_DEV
+#else
+#define RTC_CHAIN_ATTR static __device__ __noinline__
+#endif
+#ifndef RTC_SLAB_RCP_APPROX
+#define RTC_SLAB_RCP_APPROX 1
+#endif
+#ifndef RTC_MEDIA_FAST
+#define RTC_MEDIA_FAST 1
+#endif
 #ifndef RTC_SLAB_ONE_FMA
 #define RTC_SLAB_ONE_FMA 1
 #endif
@@ -35,7 +49,9 @@ struct Ray {
 };
 
 /* world (or enclosing-frame) ray -> object frame, op by op like Translate_hit / RotateY_hit (hittable.c:325-367) */
-RTC_DEV Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
+/* (out of line: entering an instance is rare next to a node visit, and the kernels are instruction-cache bound on
+ * the scenes that have instances -- see DESIGN.md) */
+RTC_CHAIN_ATTR Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
   for (uint32_t k = 0; k < op_count; k++) {
     const float4 op = __ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k]));
     if (__float_as_uint(op.w) == 0u) {
@@ -48,7 +64,7 @@ RTC_DEV Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, 
   return r;
 }
 /* object frame -> world for a hit point and its normal, innermost op first */
-RTC_DEV void chain_unapply(const DScene &sc, uint32_t op_begin, uint32_t op_count, V3 &p, V3 &n) {
+RTC_CHAIN_ATTR void chain_unapply(const DScene &sc, uint32_t op_begin, uint32_t op_count, V3 &p, V3 &n) {
   for (uint32_t k = op_count; k-- > 0;) {
     const float4 op = __ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k]));
     if (__float_as_uint(op.w) == 0u) {
@@ -92,22 +108,31 @@ struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * i
   V3 inv, oi;
   float slack; /* bound on the rounding error of an interval comparison made with those t's */
 };
+/* 1/d for the box test only (hit distances never use it): the 1-ulp hardware reciprocal, one MUFU instead of the
+ * ~10 instructions plus slow path of an IEEE division -- the relative slack of slab_test covers the extra half ulp. */
+RTC_DEV float slab_inv(float d) {
+  const float qnan = __int_as_float(0x7fc00000);
+  float inv;
+#if RTC_SLAB_RCP_APPROX
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d)); /* denormal d -> inf, capped below; |d| > 2^126 -> 0 */
+#else
+  inv = 1.0f / d;
+#endif
+  return d == 0.0f ? qnan : copysignf(fminf(fabsf(inv), 1e30f), d);
+}
 RTC_DEV SlabRay slab_setup(const Ray &r) {
   SlabRay s;
   /* |1/d| is capped at 1e30 so that plane*inv and o*inv never overflow to inf - inf (scene coordinates are far
    * below 3e8).  A component of EXACTLY zero gets NaN: both planes of that axis then drop out of fminf/fmaxf, i.e.
    * the axis is ignored, which errs on the side of visiting.  (The reference's (plane - o) * inf also yields NaN
    * when the ray lies in a face plane -- hittable.c:40-42 -- and a finite stand-in would turn that into a miss.) */
-  const float qnan = __int_as_float(0x7fc00000);
-  s.inv = v3(r.d.x == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.x), 1e30f), r.d.x),
-             r.d.y == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.y), 1e30f), r.d.y),
-             r.d.z == 0.0f ? qnan : copysignf(fminf(fabsf(1.0f / r.d.z), 1e30f), r.d.z));
+  s.inv = v3(slab_inv(r.d.x), slab_inv(r.d.y), slab_inv(r.d.z));
   s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
   /* plane*inv - o*inv cancels: each t carries an ABSOLUTE error of about eps * |o*inv| (o*inv and inv are already
    * rounded), which for coordinates in the hundreds is as large as the reference's 1e-4 padding of flat boxes.  Two
-   * such errors meet in `enter <= leave`, so the exit distance is widened by 3e-7 * max|o*inv| (NaN axes drop out):
-   * a box the exact ray touches is never culled. */
-  s.slack = 3e-7f * fmaxf(fmaxf(fabsf(s.oi.x), fabsf(s.oi.y)), fabsf(s.oi.z));
+   * such errors meet in `enter <= leave`, so the exit distance is widened by 5e-7 * max|o*inv| (NaN axes drop out):
+   * a box the exact ray touches is never culled.  (Budget per t: inv 1 ulp = 1.2e-7, o*inv another 6e-8.) */
+  s.slack = 5e-7f * fmaxf(fmaxf(fabsf(s.oi.x), fabsf(s.oi.y)), fabsf(s.oi.z));
   return s;
 }
 
@@ -123,8 +148,9 @@ RTC_DEV bool slab_test(const SlabRay &s, float xlo, float xhi, float ylo, float 
   enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
   float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
   /* NONNEG: the caller's t_min is >= 0, so a negative exit distance is a miss whatever the slack does to it and
-   * one FMA serves (leave * (1 + 4e-7) only widens a non-negative exit) */
-  leave = (NONNEG && RTC_SLAB_ONE_FMA) ? fmaf(leave, 1.0000004f, s.slack) : fmaf(fabsf(leave), 4e-7f, leave) + s.slack;
+   * one FMA serves (leave * (1 + 6e-7) only widens a non-negative exit).  6e-7 relative: the two axes that meet in
+   * the comparison each carry inv (1.2e-7) and the FMA's rounding (6e-8), and so does the entry side. */
+  leave = (NONNEG && RTC_SLAB_ONE_FMA) ? fmaf(leave, 1.0000006f, s.slack) : fmaf(fabsf(leave), 6e-7f, leave) + s.slack;
   return enter <= leave;
 }
 
@@ -294,7 +320,7 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
     const bool in = w.at_inner();
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
-    if (in) { /* two visits per vote: halves the cost of voting */
+    if (in) { /* (RTC_VISITS_PER_VOTE = 2 halves the votes but measured slower: code size) */
       w.visit<NONNEG>(sc, t_min, outer);
       if (RTC_VISITS_PER_VOTE > 1 && w.at_inner())
         w.visit<NONNEG>(sc, t_min, outer);
@@ -328,6 +354,34 @@ static __device__ __noinline__ TraceHit trace_group_call(const DScene &sc, uint3
   return trace_group(sc, root, r, t_min, t_max);
 }
 
+/* Sphere_hit (hittable.c:125-146) asked twice the way ConstantMedium_hit asks its boundary (hittable.c:396-401):
+ * over (-inf, inf), then over (t_in + 0.0001, inf).  Same arithmetic, same accept/reject tests, evaluated once. */
+RTC_DEV bool sphere_boundary(V3 center, float radius, V3 o, V3 d, float &t_in, float &t_out) {
+  V3 oc = sv_sub(o, center);
+  float a = sv_len2(d);
+  float b = sv_dot(oc, d);
+  float c = s_sub(sv_len2(oc), s_mul(radius, radius));
+  float disc = s_sub(s_mul(b, b), s_mul(a, c));
+  if (disc < 0.0f)
+    return false;
+  float sq = __fsqrt_rn(disc);
+  const float r1 = s_div(s_sub(-b, sq), a), r2 = s_div(s_add(-b, sq), a);
+  t_in = r1;
+  if (r1 <= -RTC_INF || r1 >= RTC_INF) {
+    t_in = r2;
+    if (r2 <= -RTC_INF || r2 >= RTC_INF)
+      return false;
+  }
+  const float t_min = s_add(t_in, 0.0001f);
+  t_out = r1;
+  if (r1 <= t_min || r1 >= RTC_INF) {
+    t_out = r2;
+    if (r2 <= t_min || r2 >= RTC_INF)
+      return false;
+  }
+  return true;
+}
+
 /* ConstantMedium_hit (hittable.c:392-423) for every medium of the scene, after the surfaces: two boundary
  * queries, one draw when the clipped interval is not empty. */
 template <bool EXACT>
@@ -335,12 +389,21 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
   for (uint32_t m = 0; m < sc.n_media; m++) {
     const MMedium *med = &sc.media[m];
     Ray r = chain_apply(sc, med->op_begin, med->op_count, world);
-    TraceHit in = trace_group_call(sc, med->root, r, -RTC_INF, RTC_INF);
-    if (in.prim == PRIM_NONE)
-      continue;
-    TraceHit out = trace_group_call(sc, med->root, r, s_add(in.t, 0.0001f), RTC_INF);
-    if (out.prim == PRIM_NONE)
-      continue;
+    TraceHit in, out;
+    const uint32_t root = med->root;
+    if (RTC_MEDIA_FAST && REF_KIND(root) == REF_SPHERES && REF_COUNT(root) == 1) {
+      /* boundary = one sphere (the reference's fog and smoke balls): both queries share b, c and the square root */
+      const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[REF_INDEX(root)]));
+      if (!sphere_boundary(v3(s.x, s.y, s.z), s.w, r.o, r.d, in.t, out.t))
+        continue;
+    } else {
+      in = trace_group_call(sc, root, r, -RTC_INF, RTC_INF);
+      if (in.prim == PRIM_NONE)
+        continue;
+      out = trace_group_call(sc, root, r, s_add(in.t, 0.0001f), RTC_INF);
+      if (out.prim == PRIM_NONE)
+        continue;
+    }
     float in_t = fmaxf(in.t, t_min), out_t = fminf(out.t, best.t);
     if (in_t >= out_t)
       continue;
