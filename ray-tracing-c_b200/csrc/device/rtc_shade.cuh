@@ -45,6 +45,11 @@ template <bool EXACT, bool WANT_UV> RTC_DEV void sphere_record(V3 center, float 
     rec.v = m_acos<EXACT>(-outward.y) * RTC_1_PI;
   }
 }
+/* the (u, v) part alone, from the outward normal (hittable.c:118-123) */
+template <bool EXACT> RTC_DEV void sphere_uv(V3 outward, Hit &rec) {
+  rec.u = (m_atan2<EXACT>(-outward.z, outward.x) + RTC_PI) * RTC_1_PI * 0.5f;
+  rec.v = m_acos<EXACT>(-outward.y) * RTC_1_PI;
+}
 
 template <bool EXACT> RTC_DEV bool sphere_hit(const rt_sphere &s, V3 o, V3 d, float t_min, float t_max, Hit &rec) {
   V3 center = v_load(s.center);

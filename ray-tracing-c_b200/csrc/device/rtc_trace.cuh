@@ -76,6 +76,17 @@ RTC_CHAIN_ATTR void chain_unapply(const DScene &sc, uint32_t op_begin, uint32_t 
   }
 }
 
+/* out-of-line copies for the once-per-segment users (hit record, media): the render kernels are instruction-cache
+ * bound on scenes with instances and media (ncu: "no instruction" is their first stall reason), and a call per
+ * segment is nothing next to the ~20 node visits of that segment */
+static __device__ __noinline__ Ray chain_apply_call(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
+  return chain_apply(sc, op_begin, op_count, r);
+}
+static __device__ __noinline__ void chain_unapply_call(const DScene &sc, uint32_t op_begin, uint32_t op_count, V3 &p,
+                                                       V3 &n) {
+  chain_unapply(sc, op_begin, op_count, p, n);
+}
+
 /* One 64-byte BNode.  WIDE: two 256-bit read-only loads (LDG.E.256, sm_100+) instead of four 128/64-bit ones --
  * half the load instructions and half the L1 wavefronts of the node loop.  Only the kernels' own inlined node loops
  * use it: ptxas 12.9 crashes on a 256-bit load inside a device FUNCTION that two kernels of a module call
@@ -388,7 +399,7 @@ template <bool EXACT>
 __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, float t_min, TraceHit &best, Rng &g) {
   for (uint32_t m = 0; m < sc.n_media; m++) {
     const MMedium *med = &sc.media[m];
-    Ray r = chain_apply(sc, med->op_begin, med->op_count, world);
+    Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
     TraceHit in, out;
     const uint32_t root = med->root;
     if (RTC_MEDIA_FAST && REF_KIND(root) == REF_SPHERES && REF_COUNT(root) == 1) {
@@ -425,10 +436,10 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
   const uint32_t kind = REF_KIND(h.prim), idx = REF_INDEX(h.prim);
   if (kind == PRIM_MEDIUM_KIND) { /* only t, p, material (hittable.c:418-422) */
     const MMedium *med = &sc.media[idx];
-    Ray r = chain_apply(sc, med->op_begin, med->op_count, world);
+    Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
     rec.p = sv_at(r.o, r.d, h.t);
     rec.n = v3(0, 0, 0);
-    chain_unapply(sc, med->op_begin, med->op_count, rec.p, rec.n);
+    chain_unapply_call(sc, med->op_begin, med->op_count, rec.p, rec.n);
     rec.material = med->material;
     rec.node = med->node;
     rec.u = rec.v = 0.0f;
@@ -440,7 +451,7 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
   if (h.inst != RT_NONE) {
     const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[h.inst]));
     op_begin = inst.x, op_count = inst.y;
-    r = chain_apply(sc, op_begin, op_count, world);
+    r = chain_apply_call(sc, op_begin, op_count, world);
   }
   if (kind == REF_SPHERES) {
     const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[idx]));
@@ -449,10 +460,9 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
     rec.node = meta.y;
     rec.u = rec.v = 0.0f;
     const uint32_t tex = __ldg(&sc.materials[meta.x].texture);
-    if (EXACT || texture_needs_uv(sc, tex))
-      sphere_record<EXACT, true>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
-    else
-      sphere_record<EXACT, false>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
+    sphere_record<EXACT, false>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
+    if (EXACT || texture_needs_uv(sc, tex)) /* (u, v) cost an atan2 and an acos: only for textures that read them */
+      sphere_uv<EXACT>(rec.front ? rec.n : v_neg(rec.n), rec);
   } else {
     const MQuad *q = &sc.mquads[idx];
     const float4 n_D = __ldg(&q->n_D), q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar),
@@ -468,7 +478,7 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
     rec.n = rec.front ? nrm : v_neg(nrm);
   }
   if (op_count)
-    chain_unapply(sc, op_begin, op_count, rec.p, rec.n);
+    chain_unapply_call(sc, op_begin, op_count, rec.p, rec.n);
 }
 
 /* The integrator's query (raytracing.c:45): surfaces, then media. */
