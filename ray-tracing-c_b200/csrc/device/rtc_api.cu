@@ -80,10 +80,41 @@ struct DeviceGuard {
   }
 };
 
+/* Device memory comes from the device's stream-ordered pool with its release threshold raised, so that the
+ * create / render / destroy cycle of Camera_render (one scene per call, like the reference) reuses the same pages:
+ * with plain cudaMalloc / cudaFree the driver hands the ~100 MB of per-chunk partial sums back to the OS at every
+ * destroy, and one call in three then stalled for 30-400 ms in the next allocation (measured, Book 1 final). */
+static cudaError_t dev_alloc(void **ptr, size_t bytes) {
+  static bool pool_ready[64] = {false};
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess)
+    return err;
+  if (dev >= 0 && dev < 64 && !pool_ready[dev]) {
+    cudaMemPool_t pool;
+    err = cudaDeviceGetDefaultMemPool(&pool, dev);
+    if (err != cudaSuccess)
+      return err;
+    unsigned long long keep = ~0ull;
+    err = cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    if (err != cudaSuccess)
+      return err;
+    pool_ready[dev] = true;
+  }
+  err = cudaMallocAsync(ptr, bytes, (cudaStream_t)0);
+  if (err != cudaSuccess)
+    return err;
+  return cudaStreamSynchronize((cudaStream_t)0); /* callers use the memory from other streams right away */
+}
+static void dev_free(void *ptr) {
+  if (ptr)
+    cudaFreeAsync(ptr, (cudaStream_t)0); /* the legacy default stream orders this after all earlier work */
+}
+
 template <typename T> int upload(rt_scene *s, const T *host, size_t count, const T **out) {
   size_t bytes = (count ? count : 1) * sizeof(T);
   void *dev = nullptr;
-  CUDA_TRY(cudaMalloc(&dev, bytes));
+  CUDA_TRY(dev_alloc(&dev, bytes));
   s->allocations.push_back(dev);
   if (count)
     CUDA_TRY(cudaMemcpy(dev, host, count * sizeof(T), cudaMemcpyHostToDevice));
@@ -96,11 +127,13 @@ template <typename T> int upload(rt_scene *s, const T *host, size_t count, const
 int ensure(void **ptr, size_t *have, size_t need) {
   if (*have >= need && *ptr)
     return RT_OK;
-  if (*ptr)
-    cudaFree(*ptr);
+  if (*ptr) {
+    cudaDeviceSynchronize(); /* the old buffer may still be in use on a caller's stream */
+    dev_free(*ptr);
+  }
   *ptr = nullptr;
   *have = 0;
-  CUDA_TRY(cudaMalloc(ptr, need ? need : 16));
+  CUDA_TRY(dev_alloc(ptr, need ? need : 16));
   *have = need;
   return RT_OK;
 }
@@ -111,16 +144,13 @@ extern "C" void rt_scene_destroy(rt_scene *scene) {
   if (!scene)
     return;
   DeviceGuard guard(scene->device);
+  cudaDeviceSynchronize(); /* renders enqueued on caller streams (rt_render_device) may still be running */
   for (void *p : scene->allocations)
-    cudaFree(p);
-  if (scene->counters)
-    cudaFree(scene->counters);
-  if (scene->scratch)
-    cudaFree(scene->scratch);
-  if (scene->radiance)
-    cudaFree(scene->radiance);
-  if (scene->rgb8)
-    cudaFree(scene->rgb8);
+    dev_free(p);
+  dev_free(scene->counters);
+  dev_free(scene->scratch);
+  dev_free(scene->radiance);
+  dev_free(scene->rgb8);
   for (cudaEvent_t e : scene->ev)
     if (e)
       cudaEventDestroy(e);
@@ -192,7 +222,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   v.world_root = built.world_root;
   v.n_media = (uint32_t)built.media.size();
   if (rc == RT_OK) {
-    cudaError_t err = cudaMalloc(&s->counters, sizeof(RenderCounters));
+    cudaError_t err = dev_alloc((void **)&s->counters, sizeof(RenderCounters));
     for (int k = 0; k < 4 && err == cudaSuccess; k++)
       err = cudaEventCreate(&s->ev[k]);
     if (err != cudaSuccess)
