@@ -40,8 +40,9 @@ UNIT = "Mseg/s"
 SCENE_ID, WIDTH, SPP, DEPTH = 1, 1200, 1000, 50
 REF_FAST = ROOT / "oracle" / "_ref" / "ref_main_fast"
 # dram__bytes_read.sum + dram__bytes_write.sum of mega_render_kernel per launch, from profiles/ (ncu --set full);
-# None until a capture of the current kernel exists
-NCU_DRAM_BYTES_PER_LAUNCH = None
+# profiles/r01f_mega_render_kernel_book1_1000spp.txt (the bench's own launch: 1200x675, 1000 spp): 22.05 MB read +
+# 4.989 GB written -- local-memory (traversal stack, spills) write-backs from L2, 18.6 GB/s, 0.23 % of DRAM peak
+NCU_DRAM_BYTES_PER_LAUNCH = 5.011e9
 FALLBACK_FLOP_PER_SEGMENT = 1434.0  # scene 1; recomputed live from the oracle's counters when possible
 
 
@@ -313,9 +314,9 @@ def b200_arm(args):
     except (OSError, ValueError):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    # compulsory HBM bytes of one launch: the per-chunk partial sums written once + read once + the summed frame
-    chunks = max(1, min(64, (cam.samples_per_pixel // world) // 8))
-    hbm_bytes = n_values * 4 * (2 * chunks + 1)
+    # compulsory HBM bytes of one launch: the scene read once and the summed frame written once (the per-chunk partial
+    # sums, 12 frames for this configuration, live in L2-sized buffers and are an implementation choice)
+    hbm_bytes = n_values * 4 + int(info["device_bytes"])
     roofline = {
         "bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
         "frac": achieved_tflops / fp32_peak if fp32_peak > 0 else None,
