@@ -74,11 +74,17 @@ def kernel(report, index=0):
     for key in RAW_KEYS:
         if key in col:
             print(f"{key:75s} {values[col[key]]:>18s} {units[col[key]]}")
-    print("\n# warp stall reasons (per warp active, %)")
+    print("\n# warp stall reasons (warps stalled per issued instruction; 'selected' = 1 is the issuing warp)")
+    def num(v):
+        try:
+            return float(str(v).replace(",", ""))
+        except ValueError:
+            return 0.0
     stalls = [(h, values[i]) for h, i in col.items()
-              if h.startswith("smsp__warp_issue_stalled_") and h.endswith("_per_warp_active.pct")]
-    for h, v in sorted(stalls, key=lambda kv: -float(kv[1] or 0))[:10]:
-        print(f"{h:75s} {v:>18s}")
+              if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
+    for h, v in sorted(stalls, key=lambda kv: -num(kv[1]))[:8]:
+        name = h[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]
+        print(f"  {name:28s} {num(v):6.2f}")
 
     src = ncu_csv(report, "source")
     # the first kernel's table: row 0 = kernel name, row 1 = header
