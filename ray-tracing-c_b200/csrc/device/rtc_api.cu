@@ -342,7 +342,10 @@ static int enqueue_render(rt_scene *s, const rt_camera *cam, const rt_opts *opts
     if (!s->mega_ok)
       return fail(RT_ERR_UNSUPPORTED, "render: %s (use RT_KERNEL_EXACT)", s->mega_why.c_str());
     MegaPlan plan;
-    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, &plan));
+    const int scene_class = s->view.n_media           ? MEGA_SCENE_MEDIA
+                            : s->built_info.n_mquads ? MEGA_SCENE_QUADS
+                                                     : MEGA_SCENE_SPHERES;
+    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, scene_class, &plan));
     rc = ensure(&s->scratch, &s->scratch_bytes, plan.partial_bytes);
     if (rc != RT_OK)
       return rc;

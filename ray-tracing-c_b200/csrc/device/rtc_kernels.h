@@ -50,7 +50,10 @@ struct MegaPlan {
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */
 };
-cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, MegaPlan *plan);
+/* what the scene contains, as far as the choice of kernel variant goes (rtc_mega.cu: mega_variant) */
+enum { MEGA_SCENE_SPHERES = 0, MEGA_SCENE_QUADS = 1, MEGA_SCENE_MEDIA = 2 };
+cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, int scene_class,
+                      MegaPlan *plan);
 cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
                         cudaStream_t stream, int *launches);
 cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t stream);

@@ -26,7 +26,6 @@
 #include <cstdlib>
 
 #define MEGA_BLOCK 128
-#define MEGA_NV_DEFAULT 0   /* measured: see DESIGN.md */
 #define MEGA_THR8_DEFAULT 2 /* measured: see DESIGN.md */
 
 RTC_DEV bool has_nan3(V3 a) { return a.x != a.x || a.y != a.y || a.z != a.z; }
@@ -153,8 +152,12 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
 
 /* MINB = resident CTAs per SM the register allocation must allow (occupancy vs spills; chosen from measurements,
  * RT_MEGA_MINB overrides for tuning) */
-template <int MINB>
-__global__ void __launch_bounds__(MEGA_BLOCK, MINB)
+/* BLOCK / LOCKSTEP: the default is 128-thread CTAs whose warps run freely.  LOCKSTEP puts a CTA-wide barrier between
+ * the phases, so that all warps of a (large) CTA execute the same phase at the same time: on scenes that use every
+ * code path (Book 2 final) the kernel is instruction-cache bound, and one phase's code fits the cache where the whole
+ * loop body does not. */
+template <int MINB, int BLOCK, bool LOCKSTEP>
+__global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
   /* per-lane counts of one launch: a lane would need days to overflow 32 bits */
@@ -203,8 +206,8 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
           s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
       }
     }
-    /* warp-uniform exit, and the point where all 32 lanes meet again before the traversal */
-    if (__all_sync(0xffffffffu, done))
+    /* warp-uniform (CTA-uniform) exit, and the point where all lanes meet again before the traversal */
+    if (LOCKSTEP ? __syncthreads_and(done) : __all_sync(0xffffffffu, done))
       break;
 
     /* ---- phase 2: one closest-hit query for every live lane, entered together */
@@ -224,7 +227,10 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
       if (sc.n_media)
         trace_media<false>(sc, ray, 1e-3f, th, rng);
     }
-    __syncwarp();
+    if (LOCKSTEP)
+      __syncthreads();
+    else
+      __syncwarp();
 
     /* ---- phase 3: shade.  The radiance of a path stays 0 until the step that ends it (emission or background),
      * so it is not part of the state a lane carries through the walk. */
@@ -460,32 +466,40 @@ __global__ void mega_sum_chunks_kernel(const float *__restrict__ partial, float 
 
 typedef void (*MegaKernel)(const DScene, const RenderJob, const MegaPlan, float *);
 struct MegaVariant {
-  int nv, minb; /* nv = 0: one path per lane (registers) */
+  int nv, minb; /* nv = 0: one path per lane (registers); nv = -1: the same in lockstep CTAs */
   MegaKernel fn;
   size_t smem;
+  int block;
 };
 static const MegaVariant mega_variants[] = {
-    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>()}, /* first entry of an nv = its default */
-    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>()},
-    {0, 8, mega_render_kernel<8>, 0},
-    {0, 6, mega_render_kernel<6>, 0},
-    {0, 4, mega_render_kernel<4>, 0},
+    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK}, /* first entry of an nv = its default */
+    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
+    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
+    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
+    {-1, 4, mega_render_kernel<4, 256, true>, 0, 256},
+    {-1, 2, mega_render_kernel<2, 512, true>, 0, 512},
+    {-1, 1, mega_render_kernel<1, 1024, true>, 0, 1024},
 };
 static int env_int(const char *name, int fallback) {
   const char *v = getenv(name);
   return v ? atoi(v) : fallback;
 }
-/* RT_MEGA_NV (paths per lane, 0 = the register kernel) and RT_MEGA_MINB (CTAs per SM the registers must allow) pick
- * the variant; a combination that is not built falls back to the nv's default minb, then to the default variant. */
-static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks) {
-  static int nv = -1, minb = -1;
-  if (nv < 0) {
-    nv = env_int("RT_MEGA_NV", MEGA_NV_DEFAULT);
-    minb = env_int("RT_MEGA_MINB", 0);
+/* Which kernel renders a scene.  Default, from measurements on the eight reference scenes: free-running
+ * 128-thread CTAs for sphere-only scenes; lockstep CTAs of 256 threads once the scene has quads (Cornell +5 %, the
+ * quad scene +12 %), of 512 threads once it has media (Book 2 final +34 %: instruction cache).  RT_MEGA_NV (paths per
+ * lane: 0 = free-running register kernel, -1 = lockstep, 2/4 = warp ray queue) and RT_MEGA_MINB (CTAs per SM the
+ * registers must allow) override; a combination that is not built falls back to the nv's first entry. */
+static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class) {
+  int nv = env_int("RT_MEGA_NV", -99), minb = env_int("RT_MEGA_MINB", 0);
+  if (nv == -99) {
+    nv = scene_class == MEGA_SCENE_SPHERES ? 0 : -1;
+    if (minb == 0 && nv == -1)
+      minb = scene_class == MEGA_SCENE_MEDIA ? 2 : 4;
   }
   int want_nv = nv;
   /* the slot layout packs the pixel into 16+16 bits, the depth into 16 and the chunk into 8 */
-  if (cam.img_width > 65535 || cam.img_height > 65535 || cam.max_depth > 65535 || n_chunks > 256)
+  if (want_nv > 0 && (cam.img_width > 65535 || cam.img_height > 65535 || cam.max_depth > 65535 || n_chunks > 256))
     want_nv = 0;
   const int n = (int)(sizeof(mega_variants) / sizeof(mega_variants[0]));
   for (int pass = 0; pass < 2; pass++)
@@ -498,27 +512,28 @@ static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks) {
   return &mega_variants[0];
 }
 
-cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, MegaPlan *plan) {
+cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, int scene_class,
+                      MegaPlan *plan) {
   int sms = 0, per_sm = 0;
   cudaError_t err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (err != cudaSuccess)
     return err;
   /* chunking first (the variant depends on it only through a capacity check); the grid size is needed for the
    * chunk count, so take the default variant's occupancy for that estimate */
-  const MegaVariant *var = mega_variant(cam, 1);
+  const MegaVariant *var = mega_variant(cam, 1, scene_class);
   if (var->smem > 48 * 1024) {
     err = cudaFuncSetAttribute(var->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)var->smem);
     if (err != cudaSuccess)
       return err;
   }
-  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, MEGA_BLOCK, var->smem);
+  err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, var->block, var->smem);
   if (err != cudaSuccess)
     return err;
   if (per_sm < 1)
     per_sm = 1;
   plan->blocks = sms * per_sm;
-  plan->threads = MEGA_BLOCK;
-  const long long paths = (long long)plan->blocks * MEGA_BLOCK * (var->nv > 0 ? var->nv : 1);
+  plan->threads = var->block;
+  const long long paths = (long long)plan->blocks * var->block * (var->nv > 0 ? var->nv : 1);
   const long long pixels = (long long)cam.img_width * cam.img_height;
   int n_chunks = 1;
   if (rng_mode == RT_RNG_SAMPLE && pixels > 0) {
@@ -538,12 +553,13 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   plan->chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->n_chunks = plan->chunk > 0 ? (sample_count + plan->chunk - 1) / plan->chunk : 1;
   plan->partial_bytes = plan->n_chunks > 1 ? (size_t)plan->n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
-  if (mega_variant(cam, plan->n_chunks) != var) { /* capacity check failed: the register kernel, its own grid */
-    var = mega_variant(cam, plan->n_chunks);
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, MEGA_BLOCK, var->smem);
+  if (mega_variant(cam, plan->n_chunks, scene_class) != var) { /* capacity check failed: the register kernel */
+    var = mega_variant(cam, plan->n_chunks, scene_class);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, var->block, var->smem);
     if (err != cudaSuccess)
       return err;
     plan->blocks = sms * (per_sm < 1 ? 1 : per_sm);
+    plan->threads = var->block;
   }
   plan->variant = (int)(var - mega_variants);
   {
