@@ -193,6 +193,29 @@ def test_render_is_deterministic(rtc, gpu_scene):
     assert st_a["segments"] == st_b["segments"]
 
 
+@pytest.mark.parametrize("scene_id", [1, 6, 7])
+def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, monkeypatch):
+    """Free-running, lockstep-CTA and warp-ray-queue kernels, voted and plain node loops: the schedule of the work
+    changes, the arithmetic of a sample and the order in which a work item sums its samples do not -- so the float
+    radiance must be identical bit for bit, and so must the segment counts."""
+    sess, desc, scene = gpu_scene(scene_id, 96, 32)
+    opts = rtc.make_opts(kernel="mega", rng="sample")
+    monkeypatch.setenv("RT_MEGA_CHUNKS", "2")  # same chunking for every variant
+    monkeypatch.setenv("RT_MEGA_NV", "0")
+    monkeypatch.setenv("RT_MEGA_MINB", "8")
+    rgb_ref, rad_ref, st_ref = scene.render(sess.camera, opts)
+    variants = [("0", "6", "2"), ("0", "4", "0"), ("-1", "4", "2"), ("-1", "2", "2"), ("-1", "1", "4"),
+                ("2", "6", "2"), ("4", "4", "0")]
+    for nv, minb, thr8 in variants:
+        monkeypatch.setenv("RT_MEGA_NV", nv)
+        monkeypatch.setenv("RT_MEGA_MINB", minb)
+        monkeypatch.setenv("RT_MEGA_THR8", thr8)
+        rgb, rad, st = scene.render(sess.camera, opts)
+        assert same_bits(rad, rad_ref).all(), (nv, minb, thr8)
+        assert np.array_equal(rgb, rgb_ref)
+        assert st["segments"] == st_ref["segments"] and st["samples"] == st_ref["samples"]
+
+
 def test_sample_ranges_add_up(rtc, gpu_scene):
     sess, desc, scene = gpu_scene(6, 64, 32)
     cam = sess.camera
