@@ -165,10 +165,13 @@ RTC_DEV bool slab_test(const SlabRay &s, float xlo, float xhi, float ylo, float 
   return enter <= leave;
 }
 
-/* sphere_isect with t_max INCLUDED, so that the traversal can see exact ties and resolve them like the reference */
-RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float t_min, float t_max, float *t) {
+/* sphere_isect with t_max INCLUDED, so that the traversal can see exact ties and resolve them like the reference.
+ * `a` = |d|^2 in the reference's operation order (sv_len2), computed once per ray frame by the caller.  The far root
+ * is only computed when the near one is behind t_min: both are monotone in the same rounded operands
+ * (fl((-b+sq)/a) >= fl((-b-sq)/a) for a > 0), so a near root beyond t_max already decides the miss -- the accept /
+ * reject outcome and the accepted bits are the reference's (hittable.c:125-137). */
+RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float a, float t_min, float t_max, float *t) {
   V3 oc = sv_sub(o, center);
-  float a = sv_len2(d);
   float b = sv_dot(oc, d);
   float c = s_sub(sv_len2(oc), s_mul(radius, radius));
   float disc = s_sub(s_mul(b, b), s_mul(a, c));
@@ -176,7 +179,9 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float t_mi
     return false;
   float sq = __fsqrt_rn(disc);
   float root = s_div(s_sub(-b, sq), a);
-  if (root <= t_min || root > t_max) {
+  if (root > t_max)
+    return false;
+  if (root <= t_min) {
     root = s_div(s_add(-b, sq), a);
     if (root <= t_min || root > t_max)
       return false;
@@ -186,14 +191,14 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float t_mi
 }
 
 /* Intersects the primitives of one leaf reference (spheres or quads) and keeps the closest; ties as the reference. */
-RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float t_min, uint32_t cur_inst, TraceHit &best,
-                            uint32_t &best_node) {
+RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float d_len2, float t_min, uint32_t cur_inst,
+                            TraceHit &best, uint32_t &best_node) {
   if (REF_KIND(ref) == REF_SPHERES) {
     const uint32_t first = REF_INDEX(ref), count = REF_COUNT(ref);
     for (uint32_t k = 0; k < count; k++) {
       const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
       float t;
-      if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, t_min, best.t, &t)) {
+      if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, d_len2, t_min, best.t, &t)) {
         if (t == best.t) {
           /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
            * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
@@ -249,6 +254,7 @@ struct Walker {
                          below stay in registers) */
   int sp;
   Ray r;              /* ray in the current frame (the group's own, or an instance's) */
+  float d_len2;       /* |r.d|^2 in the reference's operation order: the `a` of every sphere test of this frame */
   SlabRay slab;
   uint32_t cur;       /* subtree to look at next */
   uint32_t cur_inst;  /* instance whose frame the walk is in, RT_NONE for the group's own frame */
@@ -258,10 +264,11 @@ struct Walker {
   /* The ray in the group's own frame and t_min are not kept here: the caller passes them to every step (`outer` is
    * a callable returning that ray -- a register copy, or a reload from wherever the caller parked it). */
   RTC_DEV void begin(uint32_t root, const Ray &ray, float tmax) {
-    sp = 0, r = ray, slab = slab_setup(ray);
+    sp = 0, set_ray(ray);
     cur = root, cur_inst = RT_NONE, best_node = 0;
     best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
   }
+  RTC_DEV void set_ray(const Ray &ray) { r = ray, d_len2 = sv_len2(ray.d), slab = slab_setup(ray); }
   RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
   RTC_DEV bool done() const { return cur == REF_EMPTY; }
 
@@ -273,8 +280,7 @@ struct Walker {
       uint32_t e = stack[--sp];
       if (e != TRACE_SENTINEL)
         return e;
-      r = outer();
-      slab = slab_setup(r);
+      set_ray(outer());
       cur_inst = RT_NONE;
     }
   }
@@ -301,14 +307,13 @@ struct Walker {
   /* one leaf reference: primitives, or an instance whose frame is entered (a sentinel brings the outer ray back) */
   template <class Outer> RTC_DEV void leaf(const DScene &sc, float t_min, Outer outer) {
     if (REF_KIND(cur) != REF_INSTANCE) {
-      leaf_intersect(sc, cur, r, t_min, cur_inst, best, best_node);
+      leaf_intersect(sc, cur, r, d_len2, t_min, cur_inst, best, best_node);
     } else {
       const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
       if (inst.z != REF_EMPTY) {
         stack[sp++] = TRACE_SENTINEL;
         cur_inst = REF_INDEX(cur);
-        r = chain_apply(sc, inst.x, inst.y, outer());
-        slab = slab_setup(r);
+        set_ray(chain_apply(sc, inst.x, inst.y, outer()));
         cur = inst.z;
         return;
       }
