@@ -254,6 +254,35 @@ def test_full_size_book1_properties(rtc, gpu_scene):
     assert abs(np.clip(rad_4 / 4, 0, 1).mean() - np.clip(rad_e / 4, 0, 1).mean()) < 1.0 / 255
 
 
+@pytest.mark.parametrize("scene_id,width,size,seg_lo,seg_hi", [(6, 600, (600, 600), 2.4, 3.5),
+                                                               (7, 1000, (1000, 1000), 4.4, 6.3)])
+def test_full_size_cornell_and_book2_properties(rtc, gpu_scene, scene_id, width, size, seg_lo, seg_hi):
+    """BASELINE configs 3 and 4 geometry (600x600 Cornell with the mixture pdf, 1000x1000 Book 2 final; depth 50) at
+    8 spp: the same size-independent properties as config 2 -- sample and segment accounting (2.93 and
+    5.32 segments per sample), finite radiance, sample ranges add up, reruns are bit-identical, and the picture agrees
+    with the exact kernel's (which is the oracle's, bit for bit)."""
+    sess, desc, scene = gpu_scene(scene_id, width, 8)
+    cam = sess.camera
+    assert (cam.img_width, cam.img_height, cam.max_depth) == (size[0], size[1], 50)
+    opts = rtc.make_opts(kernel="mega", rng="sample")
+    rgb, rad, st = scene.render(cam, opts)
+    assert st["samples"] == size[0] * size[1] * 8
+    assert seg_lo < st["segments"] / st["samples"] < seg_hi
+    assert np.isfinite(rad).all()
+    if scene_id == 6:
+        assert st["light_pdf_evals"] > 0  # the mixture pdf is exercised
+    _, lo, _ = scene.render(cam, rtc.make_opts(kernel="mega", rng="sample", sample_begin=0, sample_count=3))
+    _, hi, _ = scene.render(cam, rtc.make_opts(kernel="mega", rng="sample", sample_begin=3, sample_count=5))
+    assert np.allclose(lo + hi, rad, rtol=2e-5, atol=1e-5)
+    _, again, st2 = scene.render(cam, opts)
+    assert same_bits(again, rad).all() and st2["segments"] == st["segments"]
+    _, rad_e, _ = scene.render(cam, rtc.make_opts(kernel="exact", rng="sample", sample_count=2))
+    _, rad_2, _ = scene.render(cam, rtc.make_opts(kernel="mega", rng="sample", sample_count=2))
+    # Cornell at 2 spp is dominated by fireflies of the light sampling: compare clipped means and a loose RMSE
+    assert abs(np.clip(rad_2 / 2, 0, 1).mean() - np.clip(rad_e / 2, 0, 1).mean()) < 2.0 / 255
+    assert (_rmse(np.clip(rad_2 / 2, 0, 1), np.clip(rad_e / 2, 0, 1)) < 0.25).all()
+
+
 def test_unknown_kernel_is_refused(rtc, gpu_scene):
     sess, desc, scene = gpu_scene(0)
     with pytest.raises(rtc.lib.RtError) as err:
