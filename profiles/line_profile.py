@@ -6,7 +6,9 @@ active threads and the static size per call path -- the table DESIGN.md's "where
     python profiles/line_profile.py gpurun_out/prof.ncu-rep '_Z18mega_render_kernelILi8EEv6DScene9RenderJob8MegaPlanPf' \
         [depth=3] > profiles/rNN_paths_<kernel>.txt
 
-The library under ray-tracing-c_b200/_build must be the one that was profiled.
+The library under ray-tracing-c_b200/_build must be the one that was profiled.  Function names come from the nearest
+preceding declaration in the source file of each line record: exact for the kernel's own inlined code, approximate
+inside the out-of-line functions (bracketed regions), whose bracket label is the symbol nvdisasm prints.
 """
 import collections
 import csv
