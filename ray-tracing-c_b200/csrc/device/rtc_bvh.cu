@@ -27,8 +27,8 @@ std::string rtc_validate_desc(const rt_scene_desc &d) {
     return "objects_root out of range";
   if (d.lights_root != RT_NONE && d.lights_root >= d.n_nodes)
     return "lights_root out of range";
-  if (d.n_nodes > 0x1FFFFFFu || d.n_spheres > 0x1FFFFFFu || d.n_quads > 0x1FFFFFFu)
-    return "scene too large for 25-bit references";
+  if (d.n_nodes > 0x1FFFFFFu || d.n_spheres > REF_MAX_INDEX || d.n_quads > REF_MAX_INDEX)
+    return "scene too large for 22-bit primitive references";
 
   for (uint32_t i = 0; i < d.n_textures; i++) {
     const rt_texture &t = d.textures[i];
@@ -224,23 +224,19 @@ struct Box {
 };
 
 struct Item {
-  uint32_t kind;  /* REF_SPHERES / REF_QUADS / REF_INSTANCE */
-  uint32_t index; /* desc sphere / desc quad / built instance */
-  Box box;
+  uint32_t kind;  /* REF_SPHERES / REF_QUADS */
+  uint32_t index; /* desc sphere / desc quad */
+  uint32_t tag;   /* 0: in the group's own frame; k: under out.insts[k-1]'s transform chain */
+  Box box;        /* in the group's frame */
 };
 
 /* SAH constants: one inner visit (two box tests) = 1; tunable through the environment for experiments */
-static int env_int(const char *name, int fallback) {
-  const char *v = getenv(name);
-  return v && *v ? atoi(v) : fallback;
-}
 static float env_float(const char *name, float fallback) {
   const char *v = getenv(name);
   return v && *v ? (float)atof(v) : fallback;
 }
-static const int kMaxLeaf = std::min(32, std::max(1, env_int("RT_BVH_LEAF", 1)));
 static const float kCostNode = 1.0f, kCostSphere = env_float("RT_BVH_COST_SPHERE", 0.8f),
-                   kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f), kCostInstance = 4.0f;
+                   kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f);
 
 struct Builder {
   const rt_scene_desc &d;
@@ -253,9 +249,7 @@ struct Builder {
       b.lo[a] = n.bbox[2 * a], b.hi[a] = n.bbox[2 * a + 1];
     return b;
   }
-  static float item_cost(uint32_t kind) {
-    return kind == REF_SPHERES ? kCostSphere : kind == REF_QUADS ? kCostQuad : kCostInstance;
-  }
+  static float item_cost(uint32_t kind) { return kind == REF_SPHERES ? kCostSphere : kCostQuad; }
 
   void unsupported(const std::string &why) {
     if (out.mega_supported) {
@@ -264,64 +258,118 @@ struct Builder {
     }
   }
 
-  /* object -> enclosing frame, applied from the innermost op outwards, the way the reference bounds its
-   * instances (hittable.c:336-344 Translate, :369-389 RotateY); padded because it is re-derived in float */
-  Box chain_to_outer(Box b, const std::vector<ChainOp> &chain, size_t from) const {
-    for (size_t k = chain.size(); k-- > from;) {
+  /* object -> enclosing frame for one point, applied from the innermost op outwards (the inverse of what
+   * Translate_hit / RotateY_hit do to the ray, hittable.c:325-367) */
+  static void point_to_outer(float p[3], const std::vector<ChainOp> &chain) {
+    for (size_t k = chain.size(); k-- > 0;) {
       const ChainOp &op = chain[k];
       if (!op.is_rotate) {
-        b.lo[0] += op.f0, b.hi[0] += op.f0;
-        b.lo[1] += op.f1, b.hi[1] += op.f1;
-        b.lo[2] += op.f2, b.hi[2] += op.f2;
+        p[0] += op.f0, p[1] += op.f1, p[2] += op.f2;
       } else {
         const float sn = op.f0, cs = op.f1;
-        Box r;
-        r.reset();
-        for (int c = 0; c < 8; c++) {
-          float x = (c & 1) ? b.hi[0] : b.lo[0], y = (c & 2) ? b.hi[1] : b.lo[1], z = (c & 4) ? b.hi[2] : b.lo[2];
-          Box p;
-          p.lo[0] = p.hi[0] = cs * x + sn * z;
-          p.lo[1] = p.hi[1] = y;
-          p.lo[2] = p.hi[2] = -sn * x + cs * z;
-          r.grow(p);
-        }
-        b = r;
+        const float x = p[0], z = p[2];
+        p[0] = cs * x + sn * z;
+        p[2] = -sn * x + cs * z;
       }
     }
+  }
+  /* re-derived in float: a hit the reference computes in the object's frame lies within a few ulps of the
+   * coordinates of the transformed primitive, the pad is two orders of magnitude above that */
+  static void pad_box(Box &b) {
     for (int a = 0; a < 3; a++) {
       float pad = 1e-4f + 1e-5f * std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
       b.lo[a] -= pad, b.hi[a] += pad;
     }
+  }
+  /* box of an axis-aligned box through a chain (media bounds): its 8 corners, the way the reference bounds a
+   * RotateY (hittable.c:369-389) */
+  Box chain_to_outer(const Box &b, const std::vector<ChainOp> &chain) const {
+    Box r;
+    r.reset();
+    for (int c = 0; c < 8; c++) {
+      float p[3] = {(c & 1) ? b.hi[0] : b.lo[0], (c & 2) ? b.hi[1] : b.lo[1], (c & 4) ? b.hi[2] : b.lo[2]};
+      point_to_outer(p, chain);
+      Box q;
+      for (int a = 0; a < 3; a++)
+        q.lo[a] = q.hi[a] = p[a];
+      r.grow(q);
+    }
+    pad_box(r);
+    return r;
+  }
+  /* tight bounds of ONE transformed primitive in the group's frame: a sphere stays a sphere (RotateY and Translate
+   * are rigid), a quad is the hull of its four transformed corners */
+  Box sphere_box(const rt_sphere &s, const std::vector<ChainOp> &chain) const {
+    float c[3] = {s.center[0], s.center[1], s.center[2]};
+    point_to_outer(c, chain);
+    Box b;
+    const float r = std::fabs(s.radius);
+    for (int a = 0; a < 3; a++)
+      b.lo[a] = c[a] - r, b.hi[a] = c[a] + r;
+    pad_box(b);
+    return b;
+  }
+  Box quad_box(const rt_quad &q, const std::vector<ChainOp> &chain) const {
+    Box b;
+    b.reset();
+    for (int c = 0; c < 4; c++) {
+      float p[3];
+      for (int a = 0; a < 3; a++)
+        p[a] = q.Q[a] + ((c & 1) ? q.u[a] : 0.0f) + ((c & 2) ? q.v[a] : 0.0f);
+      point_to_outer(p, chain);
+      Box pt;
+      for (int a = 0; a < 3; a++)
+        pt.lo[a] = pt.hi[a] = p[a];
+      b.grow(pt);
+    }
+    pad_box(b);
     return b;
   }
 
   /* Collects the primitives under `id` into `items` (the group being assembled).  `chain` holds the transforms
-   * between the group's frame and the current node; a transform node closes over its subtree as ONE instance
-   * whose chain is the full list of ops (instances never nest at traversal time). */
-  void collect(uint32_t id, std::vector<Item> &group_items, std::vector<Item> *inst_items,
-               std::vector<ChainOp> &chain, std::set<uint32_t> &seen, bool in_boundary,
+   * between the group's frame and the current node and `tag` names that chain (0 = none): a Translate / RotateY node
+   * does not become a node of the tree -- its primitives join the group's ONE tree with boxes in the group's frame,
+   * each remembering the chain its own test has to apply to the ray.  (The reference never bounds its instances:
+   * Translate_hit / RotateY_hit always enter the child, hittable.c:325-367.) */
+  static constexpr uint32_t kTagPending = 0xFFFFFFFFu; /* a chain whose Instance is made by its first primitive */
+  void collect(uint32_t id, std::vector<Item> &items, std::vector<ChainOp> &chain, uint32_t &tag,
+               std::set<uint32_t> &seen, bool in_boundary,
                std::vector<std::pair<uint32_t, std::vector<ChainOp>>> &media) {
     const rt_node &n = d.nodes[id];
-    std::vector<Item> &dst = inst_items ? *inst_items : group_items;
     switch (n.kind) {
     case RT_NODE_LIST:
       for (uint32_t k = 0; k < n.b; k++)
-        collect(d.children[n.a + k], group_items, inst_items, chain, seen, in_boundary, media);
+        collect(d.children[n.a + k], items, chain, tag, seen, in_boundary, media);
       break;
     case RT_NODE_BVH:
-      collect(n.a, group_items, inst_items, chain, seen, in_boundary, media);
+      collect(n.a, items, chain, tag, seen, in_boundary, media);
       if (n.b != n.a)
-        collect(n.b, group_items, inst_items, chain, seen, in_boundary, media);
+        collect(n.b, items, chain, tag, seen, in_boundary, media);
       break;
     case RT_NODE_SPHERE:
     case RT_NODE_QUAD: {
       if (!seen.insert(id).second)
         break; /* the same object twice in one frame (BVH n==1 stores it as both children) */
+      if (tag == kTagPending) {
+        if (out.insts.size() >= REF_MAX_TAG)
+          unsupported("more than 255 distinct Translate/RotateY chains in the scene");
+        Instance inst;
+        inst.op_begin = (uint32_t)out.ops.size();
+        inst.op_count = (uint32_t)chain.size();
+        inst.pad0 = inst.pad1 = 0;
+        out.ops.insert(out.ops.end(), chain.begin(), chain.end());
+        out.insts.push_back(inst);
+        tag = std::min<uint32_t>((uint32_t)out.insts.size(), REF_MAX_TAG);
+      }
       Item it;
       it.kind = n.kind == RT_NODE_SPHERE ? REF_SPHERES : REF_QUADS;
       it.index = n.a;
-      it.box = node_box(n);
-      dst.push_back(it);
+      it.tag = tag;
+      if (tag == 0)
+        it.box = node_box(n); /* the reference's own box (quads padded, hittable.c:24-37) */
+      else
+        it.box = n.kind == RT_NODE_SPHERE ? sphere_box(d.spheres[n.a], chain) : quad_box(d.quads[n.a], chain);
+      items.push_back(it);
       break;
     }
     case RT_NODE_TRANSLATE:
@@ -330,29 +378,9 @@ struct Builder {
       op.is_rotate = n.kind == RT_NODE_ROTATE_Y;
       op.f0 = n.f[0], op.f1 = n.f[1], op.f2 = n.f[2];
       chain.push_back(op);
-      std::vector<Item> mine;
+      uint32_t my_tag = kTagPending;
       std::set<uint32_t> seen_inside;
-      collect(n.a, group_items, &mine, chain, seen_inside, in_boundary, media);
-      if (!mine.empty()) {
-        Box local;
-        local.reset();
-        for (const Item &it : mine)
-          local.grow(it.box);
-        Instance inst;
-        inst.op_begin = (uint32_t)out.ops.size();
-        inst.op_count = (uint32_t)chain.size();
-        inst.pad = 0;
-        out.ops.insert(out.ops.end(), chain.begin(), chain.end());
-        int depth = 0;
-        inst.root = build(mine, 0, mine.size(), depth);
-        blas_depth = std::max(blas_depth, depth);
-        Item it;
-        it.kind = REF_INSTANCE;
-        it.index = (uint32_t)out.insts.size();
-        it.box = chain_to_outer(local, chain, 0);
-        out.insts.push_back(inst);
-        group_items.push_back(it);
-      }
+      collect(n.a, items, chain, my_tag, seen_inside, in_boundary, media);
       chain.pop_back();
       break;
     }
@@ -366,39 +394,29 @@ struct Builder {
     }
   }
 
-  int blas_depth = 0;
-
-  uint32_t make_leaf(const std::vector<Item> &items, size_t lo, size_t hi) {
-    const uint32_t kind = items[lo].kind;
-    const uint32_t count = (uint32_t)(hi - lo);
-    if (kind == REF_INSTANCE)
-      return MAKE_REF(REF_INSTANCE, 1, items[lo].index);
-    if (kind == REF_SPHERES) {
-      uint32_t first = (uint32_t)out.msph.size();
-      for (size_t k = lo; k < hi; k++) {
-        const rt_sphere &s = d.spheres[items[k].index];
-        MSphere ms = {s.center[0], s.center[1], s.center[2], s.radius};
-        MPrimMeta meta = {s.material, s.node};
-        out.msph.push_back(ms);
-        out.msph_meta.push_back(meta);
-      }
-      return MAKE_REF(REF_SPHERES, count, first);
+  uint32_t make_leaf(const Item &it) {
+    if (it.kind == REF_SPHERES) {
+      const uint32_t at = (uint32_t)out.msph.size();
+      const rt_sphere &s = d.spheres[it.index];
+      MSphere ms = {s.center[0], s.center[1], s.center[2], s.radius};
+      MPrimMeta meta = {s.material, s.node};
+      out.msph.push_back(ms);
+      out.msph_meta.push_back(meta);
+      return MAKE_REF(REF_SPHERES, it.tag, at);
     }
-    uint32_t first = (uint32_t)out.mquads.size();
-    for (size_t k = lo; k < hi; k++) {
-      const rt_quad &q = d.quads[items[k].index];
-      MQuad mq;
-      float mat_bits, node_bits;
-      memcpy(&mat_bits, &q.material, 4);
-      memcpy(&node_bits, &q.node, 4);
-      mq.n_D = make_float4(q.normal[0], q.normal[1], q.normal[2], q.D);
-      mq.q_mat = make_float4(q.Q[0], q.Q[1], q.Q[2], mat_bits);
-      mq.w_nod = make_float4(q.w[0], q.w[1], q.w[2], node_bits);
-      mq.u_ar = make_float4(q.u[0], q.u[1], q.u[2], q.area);
-      mq.v_ = make_float4(q.v[0], q.v[1], q.v[2], 0.0f);
-      out.mquads.push_back(mq);
-    }
-    return MAKE_REF(REF_QUADS, count, first);
+    const uint32_t at = (uint32_t)out.mquads.size();
+    const rt_quad &q = d.quads[it.index];
+    MQuad mq;
+    float mat_bits, node_bits;
+    memcpy(&mat_bits, &q.material, 4);
+    memcpy(&node_bits, &q.node, 4);
+    mq.n_D = make_float4(q.normal[0], q.normal[1], q.normal[2], q.D);
+    mq.q_mat = make_float4(q.Q[0], q.Q[1], q.Q[2], mat_bits);
+    mq.w_nod = make_float4(q.w[0], q.w[1], q.w[2], node_bits);
+    mq.u_ar = make_float4(q.u[0], q.u[1], q.u[2], q.area);
+    mq.v_ = make_float4(q.v[0], q.v[1], q.v[2], 0.0f);
+    out.mquads.push_back(mq);
+    return MAKE_REF(REF_QUADS, it.tag, at);
   }
 
   /* binned SAH over items[lo, hi); reorders `items` in place; returns the reference of the subtree */
@@ -408,20 +426,15 @@ struct Builder {
       return REF_EMPTY;
     Box bounds, cbounds;
     bounds.reset(), cbounds.reset();
-    bool same_kind = true;
-    float leaf_cost = 0.0f;
     for (size_t k = lo; k < hi; k++) {
       bounds.grow(items[k].box);
       Box c;
       for (int a = 0; a < 3; a++)
         c.lo[a] = c.hi[a] = 0.5f * (items[k].box.lo[a] + items[k].box.hi[a]);
       cbounds.grow(c);
-      same_kind = same_kind && items[k].kind == items[lo].kind;
-      leaf_cost += item_cost(items[k].kind);
     }
-    const bool leaf_allowed = same_kind && (items[lo].kind == REF_INSTANCE ? n == 1 : n <= (size_t)kMaxLeaf);
-    if (n == 1)
-      return make_leaf(items, lo, hi);
+    if (n == 1) /* one primitive per leaf */
+      return make_leaf(items[lo]);
 
     /* best split over 3 axes x 15 planes */
     constexpr int kBins = 16;
@@ -469,9 +482,6 @@ struct Builder {
       }
     }
 
-    if (leaf_allowed && (best_axis < 0 || leaf_cost <= best_cost))
-      return make_leaf(items, lo, hi);
-
     size_t mid;
     if (best_axis >= 0) {
       const float extent = cbounds.hi[best_axis] - cbounds.lo[best_axis];
@@ -507,7 +517,7 @@ struct Builder {
     node.child0 = c0, node.child1 = c1, node.pad0 = 0, node.pad1 = 0;
     out.bnodes[self] = node;
     depth = 1 + std::max(d0, d1);
-    return MAKE_REF(REF_INNER, 1, self);
+    return MAKE_REF(REF_INNER, 0, self);
   }
 
   /* one group = everything under `root_node` seen from that node's own frame */
@@ -516,12 +526,9 @@ struct Builder {
     std::vector<Item> items;
     std::vector<ChainOp> chain;
     std::set<uint32_t> seen;
-    blas_depth = 0;
-    collect(root_node, items, nullptr, chain, seen, in_boundary, media);
-    int tlas_depth = 0;
-    uint32_t root = build(items, 0, items.size(), tlas_depth);
-    depth = tlas_depth + 1 + blas_depth; /* +1: the sentinel that marks "leave the instance" */
-    return root;
+    uint32_t tag = 0;
+    collect(root_node, items, chain, tag, seen, in_boundary, media);
+    return build(items, 0, items.size(), depth);
   }
 };
 
@@ -547,7 +554,7 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
     mm.op_count = (uint32_t)m.second.size();
     out.ops.insert(out.ops.end(), m.second.begin(), m.second.end());
     Box nb = Builder::node_box(n);
-    Box wb = b.chain_to_outer(nb, m.second, 0);
+    Box wb = b.chain_to_outer(nb, m.second);
     for (int a = 0; a < 3; a++)
       mm.bbox[2 * a] = wb.lo[a], mm.bbox[2 * a + 1] = wb.hi[a];
     int bdepth = 0;
@@ -571,7 +578,7 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
   if (out.mquads.empty())
     out.mquads.push_back(MQuad());
   if (out.insts.empty())
-    out.insts.push_back(Instance{0, 0, REF_EMPTY, 0});
+    out.insts.push_back(Instance{0, 0, 0, 0});
   if (out.ops.empty())
     out.ops.push_back(ChainOp{0, 0, 0, 0});
   if (out.media.empty()) {

@@ -13,16 +13,22 @@
 
 /* ---- rebuilt acceleration structure (rtc_bvh.cpp builds it, rtc_mega.cu / rtc_wave.cu walk it) ---- */
 
-/* child / root reference: kind in bits 30-31, (count-1) in bits 25-29, index in bits 0-24 */
+/* child / root reference: kind in bits 30-31, instance tag in bits 22-29, index in bits 0-21.
+ * A leaf is ONE primitive (measured faster than 2 or 4 per leaf).  tag = 0: the primitive lives in the group's own
+ * frame; tag = k > 0: it lives under insts[k-1]'s transform chain -- the tree bounds it in the GROUP's frame and the
+ * leaf test moves the ray into the primitive's frame with the reference's own operation sequence, so instances cost
+ * no second traversal.  An inner reference is its node index (kind 0, tag 0). */
 #define REF_INNER 0u
 #define REF_SPHERES 1u
 #define REF_QUADS 2u
-#define REF_INSTANCE 3u
 #define REF_EMPTY 0xFFFFFFFFu
+#define REF_INDEX_BITS 22
+#define REF_MAX_INDEX ((1u << REF_INDEX_BITS) - 1u)
+#define REF_MAX_TAG 255u
 #define REF_KIND(r) ((r) >> 30)
-#define REF_COUNT(r) ((((r) >> 25) & 31u) + 1u)
-#define REF_INDEX(r) ((r)&0x1FFFFFFu)
-#define MAKE_REF(kind, count, index) (((uint32_t)(kind) << 30) | (((uint32_t)(count)-1u) << 25) | (uint32_t)(index))
+#define REF_TAG(r) (((r) >> REF_INDEX_BITS) & 255u)
+#define REF_INDEX(r) ((r)&REF_MAX_INDEX)
+#define MAKE_REF(kind, tag, index) (((uint32_t)(kind) << 30) | ((uint32_t)(tag) << REF_INDEX_BITS) | (uint32_t)(index))
 
 /* binary node holding BOTH children's boxes: two 32-byte loads per visit */
 struct __align__(32) BNode {
@@ -54,7 +60,7 @@ struct __align__(16) ChainOp {
   uint32_t is_rotate;
 };
 struct __align__(16) Instance {
-  uint32_t op_begin, op_count, root, pad;
+  uint32_t op_begin, op_count, pad0, pad1;
 };
 struct __align__(16) MMedium {
   float bbox[6];           /* world-space bound of the boundary (conservative) */

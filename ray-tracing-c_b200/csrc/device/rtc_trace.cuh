@@ -40,9 +40,8 @@
 #endif
 
 #define TRACE_STACK 48          /* rt_scene_create refuses deeper structures for the mega/wave kernels */
-#define TRACE_SENTINEL 0xFFFFFFFEu
 #define PRIM_NONE 0xFFFFFFFFu
-#define PRIM_MEDIUM_KIND 3u     /* best_prim = MAKE_REF(3, 1, medium index) for a medium hit */
+#define PRIM_MEDIUM_KIND 3u     /* best_prim = MAKE_REF(3, 0, medium index) for a medium hit */
 
 struct Ray {
   V3 o, d;
@@ -190,103 +189,90 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float a, f
   return true;
 }
 
-/* Intersects the primitives of one leaf reference (spheres or quads) and keeps the closest; ties as the reference. */
-RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float d_len2, float t_min, uint32_t cur_inst,
+/* Intersects the ONE primitive of a leaf reference (sphere or quad) and keeps it if closer; ties as the reference.
+ * `r` is the ray in the primitive's own frame, `inst` the instance that frame belongs to (RT_NONE: the group's). */
+RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float d_len2, float t_min, uint32_t inst,
                             TraceHit &best, uint32_t &best_node) {
+  const uint32_t at = REF_INDEX(ref);
   if (REF_KIND(ref) == REF_SPHERES) {
-    const uint32_t first = REF_INDEX(ref), count = REF_COUNT(ref);
-    for (uint32_t k = 0; k < count; k++) {
-      const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[first + k]));
-      float t;
-      if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, d_len2, t_min, best.t, &t)) {
-        if (t == best.t) {
-          /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
-           * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
-          if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
-            continue;
-          if (__ldg(&sc.msph_meta[first + k].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
-            continue;
-        }
-        best.t = t;
-        best.prim = MAKE_REF(REF_SPHERES, 1, first + k);
-        best.inst = cur_inst;
+    const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[at]));
+    float t;
+    if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, d_len2, t_min, best.t, &t)) {
+      if (t == best.t) {
+        /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
+         * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
+        if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
+          return;
+        if (__ldg(&sc.msph_meta[at].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
+          return;
       }
+      best.t = t;
+      best.prim = MAKE_REF(REF_SPHERES, 0, at);
+      best.inst = inst;
     }
-  } else if (REF_KIND(ref) == REF_QUADS) {
-    const uint32_t first = REF_INDEX(ref), count = REF_COUNT(ref);
-    for (uint32_t k = 0; k < count; k++) {
-      const MQuad *q = &sc.mquads[first + k];
-      const float4 n_D = __ldg(&q->n_D);
-      /* plane distance first: most candidates die here, before the other four rows are read */
-      V3 nrm = v3(n_D.x, n_D.y, n_D.z);
-      float denom = sv_dot(nrm, r.d);
-      if (fabsf(denom) < 1e-8f)
-        continue;
-      float tt = s_div(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
-      if (tt < t_min || tt > best.t)
-        continue;
-      const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
-      V3 hp = sv_sub(sv_at(r.o, r.d, tt), v3(q_mat.x, q_mat.y, q_mat.z));
-      V3 w = v3(w_nod.x, w_nod.y, w_nod.z);
-      float al = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
-      float be = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
-      if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
-        continue;
-      const uint32_t node = __float_as_uint(w_nod.w);
-      /* exact tie with an earlier candidate: the reference keeps the LATER-visited quad (closed interval,
-       * hittable.c:194) and a quad always displaces a sphere at equal t; node ids are its visiting order */
-      if (tt == best.t && best.prim != PRIM_NONE && REF_KIND(best.prim) == REF_QUADS && node < best_node)
-        continue;
-      best.t = tt;
-      best.prim = MAKE_REF(REF_QUADS, 1, first + k);
-      best.inst = cur_inst;
-      best_node = node;
-    }
+  } else {
+    const MQuad *q = &sc.mquads[at];
+    const float4 n_D = __ldg(&q->n_D);
+    /* plane distance first: most candidates die here, before the other four rows are read */
+    V3 nrm = v3(n_D.x, n_D.y, n_D.z);
+    float denom = sv_dot(nrm, r.d);
+    if (fabsf(denom) < 1e-8f)
+      return;
+    float tt = s_div(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
+    if (tt < t_min || tt > best.t)
+      return;
+    const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
+    V3 hp = sv_sub(sv_at(r.o, r.d, tt), v3(q_mat.x, q_mat.y, q_mat.z));
+    V3 w = v3(w_nod.x, w_nod.y, w_nod.z);
+    float al = sv_dot(w, sv_cross(hp, v3(v_.x, v_.y, v_.z)));
+    float be = sv_dot(w, sv_cross(v3(u_ar.x, u_ar.y, u_ar.z), hp));
+    if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f)
+      return;
+    const uint32_t node = __float_as_uint(w_nod.w);
+    /* exact tie with an earlier candidate: the reference keeps the LATER-visited quad (closed interval,
+     * hittable.c:194) and a quad always displaces a sphere at equal t; node ids are its visiting order */
+    if (tt == best.t && best.prim != PRIM_NONE && REF_KIND(best.prim) == REF_QUADS && node < best_node)
+      return;
+    best.t = tt;
+    best.prim = MAKE_REF(REF_QUADS, 0, at);
+    best.inst = inst;
+    best_node = node;
   }
 }
 
 /* State of one closest-hit query over a group.  A walker is always in one of three states: it holds an INNER node
- * (wants a two-box visit), it holds a LEAF (a primitive range, or an instance to enter), or it is done
- * (cur == REF_EMPTY).  The scheduling of visit() and leaf() steps across the lanes of a warp is the caller's:
- * trace_group() below for one ray per lane, the megakernel's warp ray queue for dynamic assignment. */
+ * (wants a two-box visit), it holds a LEAF (one primitive), or it is done (cur == REF_EMPTY).  The scheduling of
+ * visit() and leaf() steps across the lanes of a warp is the caller's: trace_group() below for one ray per lane, the
+ * megakernel's voted rounds, its warp ray queue for dynamic assignment.
+ *
+ * The whole group is ONE tree in the group's frame: primitives under Translate / RotateY nodes sit in it with boxes
+ * in the group's frame (rtc_bvh.cu), and only their own test moves the ray into their frame, op by op like
+ * Translate_hit / RotateY_hit (hittable.c:325-367) -- the hit distance keeps the reference's bits, the walk never
+ * changes frame. */
 struct Walker {
   uint32_t *stack;    /* TRACE_STACK entries owned by the caller (a separate local array, so that the scalar members
                          below stay in registers) */
   int sp;
-  Ray r;              /* ray in the current frame (the group's own, or an instance's) */
-  float d_len2;       /* |r.d|^2 in the reference's operation order: the `a` of every sphere test of this frame */
+  float d_len2;       /* |d|^2 of the group-frame ray in the reference's operation order: the `a` of its sphere tests */
   SlabRay slab;
   uint32_t cur;       /* subtree to look at next */
-  uint32_t cur_inst;  /* instance whose frame the walk is in, RT_NONE for the group's own frame */
   uint32_t best_node; /* node id of the best quad (only consulted on exact ties) */
   TraceHit best;
 
-  /* The ray in the group's own frame and t_min are not kept here: the caller passes them to every step (`outer` is
-   * a callable returning that ray -- a register copy, or a reload from wherever the caller parked it). */
+  /* The ray itself and t_min are not kept here: the caller passes them to every leaf step (`outer` is a callable
+   * returning the group-frame ray -- a register copy, or a reload from wherever the caller parked it). */
   RTC_DEV void begin(uint32_t root, const Ray &ray, float tmax) {
-    sp = 0, set_ray(ray);
-    cur = root, cur_inst = RT_NONE, best_node = 0;
+    sp = 0, d_len2 = sv_len2(ray.d), slab = slab_setup(ray);
+    cur = root, best_node = 0;
     best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
   }
-  RTC_DEV void set_ray(const Ray &ray) { r = ray, d_len2 = sv_len2(ray.d), slab = slab_setup(ray); }
   RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
   RTC_DEV bool done() const { return cur == REF_EMPTY; }
+  RTC_DEV uint32_t pop() { return sp == 0 ? REF_EMPTY : stack[--sp]; }
 
-  /* next subtree from the stack; leaving an instance (sentinel) restores the outer ray */
-  template <class Outer> RTC_DEV uint32_t pop(Outer outer) {
-    for (;;) {
-      if (sp == 0)
-        return REF_EMPTY;
-      uint32_t e = stack[--sp];
-      if (e != TRACE_SENTINEL)
-        return e;
-      set_ray(outer());
-      cur_inst = RT_NONE;
-    }
-  }
   /* one inner node: both children's boxes, nearer child first, the other one pushed */
-  template <bool NONNEG, class Outer> RTC_DEV void visit(const DScene &sc, float t_min, Outer outer) {
-    /* an inner reference is its node index (kind 0, count field 0): no masking, one multiply-add for the address;
+  template <bool NONNEG> RTC_DEV void visit(const DScene &sc, float t_min) {
+    /* an inner reference is its node index (kind 0, tag 0): no masking, one multiply-add for the address;
      * the 64-byte node arrives in two 256-bit loads */
     float4 xy0, xy1, zz;
     uint2 ch;
@@ -301,24 +287,21 @@ struct Walker {
     } else if (h0 || h1) {
       cur = h0 ? ch.x : ch.y;
     } else {
-      cur = pop(outer);
+      cur = pop();
     }
   }
-  /* one leaf reference: primitives, or an instance whose frame is entered (a sentinel brings the outer ray back) */
+  /* one leaf: the primitive is tested in its own frame */
   template <class Outer> RTC_DEV void leaf(const DScene &sc, float t_min, Outer outer) {
-    if (REF_KIND(cur) != REF_INSTANCE) {
-      leaf_intersect(sc, cur, r, d_len2, t_min, cur_inst, best, best_node);
-    } else {
-      const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[REF_INDEX(cur)]));
-      if (inst.z != REF_EMPTY) {
-        stack[sp++] = TRACE_SENTINEL;
-        cur_inst = REF_INDEX(cur);
-        set_ray(chain_apply(sc, inst.x, inst.y, outer()));
-        cur = inst.z;
-        return;
-      }
+    const uint32_t tag = REF_TAG(cur);
+    Ray r = outer();
+    float a = d_len2;
+    if (tag != 0u) {
+      const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[tag - 1u]));
+      r = chain_apply(sc, inst.x, inst.y, r);
+      a = sv_len2(r.d);
     }
-    cur = pop(outer);
+    leaf_intersect(sc, cur, r, a, t_min, tag - 1u /* RT_NONE for tag 0 */, best, best_node);
+    cur = pop();
   }
 };
 
@@ -337,9 +320,9 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
     if (in) { /* (RTC_VISITS_PER_VOTE = 2 halves the votes but measured slower: code size) */
-      w.visit<NONNEG>(sc, t_min, outer);
+      w.visit<NONNEG>(sc, t_min);
       if (RTC_VISITS_PER_VOTE > 1 && w.at_inner())
-        w.visit<NONNEG>(sc, t_min, outer);
+        w.visit<NONNEG>(sc, t_min);
     }
   }
   if (!w.at_inner() && !w.done())
@@ -357,7 +340,7 @@ RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r, floa
   auto outer = [&]() { return r; };
   for (;;) {
     while (w.at_inner())
-      w.visit<false>(sc, t_min, outer);
+      w.visit<false>(sc, t_min);
     if (w.done())
       break;
     w.leaf(sc, t_min, outer);
@@ -407,7 +390,7 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
     Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
     TraceHit in, out;
     const uint32_t root = med->root;
-    if (RTC_MEDIA_FAST && REF_KIND(root) == REF_SPHERES && REF_COUNT(root) == 1) {
+    if (RTC_MEDIA_FAST && REF_KIND(root) == REF_SPHERES && REF_TAG(root) == 0u) {
       /* boundary = one sphere (the reference's fog and smoke balls): both queries share b, c and the square root */
       const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[REF_INDEX(root)]));
       if (!sphere_boundary(v3(s.x, s.y, s.z), s.w, r.o, r.d, in.t, out.t))
@@ -430,7 +413,7 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
     if (travel > inside)
       continue;
     best.t = s_add(in_t, s_div(travel, ray_len));
-    best.prim = MAKE_REF(PRIM_MEDIUM_KIND, 1, m);
+    best.prim = MAKE_REF(PRIM_MEDIUM_KIND, 0, m);
     best.inst = RT_NONE;
   }
 }
@@ -454,7 +437,7 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
   Ray r = world;
   uint32_t op_begin = 0, op_count = 0;
   if (h.inst != RT_NONE) {
-    const uint4 inst = __ldg(reinterpret_cast<const uint4 *>(&sc.insts[h.inst]));
+    const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[h.inst]));
     op_begin = inst.x, op_count = inst.y;
     r = chain_apply_call(sc, op_begin, op_count, world);
   }

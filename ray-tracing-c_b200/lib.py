@@ -15,7 +15,8 @@ from pathlib import Path
 from . import abi
 
 PKG_DIR = Path(__file__).resolve().parent
-BUILD_DIR = PKG_DIR / "_build"
+# RTC_BUILD_DIR: a second build of the same sources (make OUT=... EXTRA=-D...) for A/B measurements
+BUILD_DIR = Path(os.environ.get("RTC_BUILD_DIR") or PKG_DIR / "_build")
 REPO_ROOT = PKG_DIR.parent
 
 # every symbol include/rtc_b200.h declares (tests check the .so exports each one)
