@@ -419,6 +419,18 @@ struct Builder {
     return MAKE_REF(REF_QUADS, it.tag, at);
   }
 
+  /* [lo, hi] as (centre, half extent) with [c - h, c + h] containing it.  The traversal computes the slab distances as
+   * fma(-+h, |1/d|, fma(c, 1/d, -o/d)): against the (lo, hi) form that is one more rounding, of the CENTRE's distance,
+   * i.e. up to 6e-8 * |c - o| in space; the |o| part is in the ray's own slack (slab_setup), the |c| part and the
+   * rounding of c and h themselves are added to h here (4e-7 |c| + 1e-6 h: generous, and nothing next to a box). */
+  static void centre_half(float lo, float hi, float &c, float &h) {
+    const double cd = 0.5 * ((double)lo + (double)hi);
+    c = (float)cd;
+    const double need = std::max((double)hi - (double)c, (double)c - (double)lo);
+    h = (float)(need * (1.0 + 1e-6) + 4e-7 * std::fabs((double)c));
+    h = std::nextafter(h, FLT_MAX);
+  }
+
   /* binned SAH over items[lo, hi); reorders `items` in place; returns the reference of the subtree */
   uint32_t build(std::vector<Item> &items, size_t lo, size_t hi, int &depth) {
     const size_t n = hi - lo;
@@ -511,9 +523,20 @@ struct Builder {
     uint32_t c0 = build(items, lo, mid, d0);
     uint32_t c1 = build(items, mid, hi, d1);
     BNode node;
+#if RTC_NODE_CH
+    float bc0[3], bh0[3], bc1[3], bh1[3];
+    for (int a = 0; a < 3; a++) {
+      centre_half(b0.lo[a], b0.hi[a], bc0[a], bh0[a]);
+      centre_half(b1.lo[a], b1.hi[a], bc1[a], bh1[a]);
+    }
+    node.xy0 = make_float4(bc0[0], bh0[0], bc0[1], bh0[1]);
+    node.xy1 = make_float4(bc1[0], bh1[0], bc1[1], bh1[1]);
+    node.zz = make_float4(bc0[2], bh0[2], bc1[2], bh1[2]);
+#else
     node.xy0 = make_float4(b0.lo[0], b0.hi[0], b0.lo[1], b0.hi[1]);
     node.xy1 = make_float4(b1.lo[0], b1.hi[0], b1.lo[1], b1.hi[1]);
     node.zz = make_float4(b0.lo[2], b0.hi[2], b1.lo[2], b1.hi[2]);
+#endif
     node.child0 = c0, node.child1 = c1, node.pad0 = 0, node.pad1 = 0;
     out.bnodes[self] = node;
     depth = 1 + std::max(d0, d1);

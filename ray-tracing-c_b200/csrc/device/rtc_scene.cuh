@@ -30,9 +30,17 @@
 #define REF_INDEX(r) ((r)&REF_MAX_INDEX)
 #define MAKE_REF(kind, tag, index) (((uint32_t)(kind) << 30) | ((uint32_t)(tag) << REF_INDEX_BITS) | (uint32_t)(index))
 
+/* RTC_NODE_CH = 1: a child's box is stored as (centre, half extent) per axis instead of (lo, hi).  The slab test then
+ * needs no pairwise min/max: near = (c - o)/d - h/|d|, far = (c - o)/d + h/|d| -- three FMAs per axis on the FMA pipe
+ * instead of two FMAs plus two FMNMX on the (half as wide, and in this kernel busiest) ALU pipe.  The half extent is
+ * rounded up and inflated by the rounding the extra subtraction can add (rtc_bvh.cu, make_node). */
+#ifndef RTC_NODE_CH
+#define RTC_NODE_CH 1
+#endif
+
 /* binary node holding BOTH children's boxes: two 32-byte loads per visit */
 struct __align__(32) BNode {
-  float4 xy0; /* child0: x.lo x.hi y.lo y.hi */
+  float4 xy0; /* child0: x.lo x.hi y.lo y.hi   (RTC_NODE_CH: x.c x.h y.c y.h) */
   float4 xy1; /* child1: x.lo x.hi y.lo y.hi */
   float4 zz;  /* child0 z.lo z.hi, child1 z.lo z.hi */
   uint32_t child0, child1, pad0, pad1;

@@ -116,6 +116,9 @@ struct TraceHit {
 
 struct SlabRay { /* per-frame constants of the box test: t = plane * inv - o * inv (one FMA per plane) */
   V3 inv, oi;
+#if RTC_NODE_CH
+  V3 ainv; /* |inv|: the half extents' distances */
+#endif
   float slack; /* bound on the rounding error of an interval comparison made with those t's */
 };
 /* 1/d for the box test only (hit distances never use it): the 1-ulp hardware reciprocal, one MUFU instead of the
@@ -138,6 +141,9 @@ RTC_DEV SlabRay slab_setup(const Ray &r) {
    * when the ray lies in a face plane -- hittable.c:40-42 -- and a finite stand-in would turn that into a miss.) */
   s.inv = v3(slab_inv(r.d.x), slab_inv(r.d.y), slab_inv(r.d.z));
   s.oi = v3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
+#if RTC_NODE_CH
+  s.ainv = v3(fabsf(s.inv.x), fabsf(s.inv.y), fabsf(s.inv.z));
+#endif
   /* plane*inv - o*inv cancels: each t carries an ABSOLUTE error of about eps * |o*inv| (o*inv and inv are already
    * rounded), which for coordinates in the hundreds is as large as the reference's 1e-4 padding of flat boxes.  Two
    * such errors meet in `enter <= leave`, so the exit distance is widened by 5e-7 * max|o*inv| (NaN axes drop out):
@@ -152,11 +158,18 @@ RTC_DEV SlabRay slab_setup(const Ray &r) {
 template <bool NONNEG>
 RTC_DEV bool slab_test(const SlabRay &s, float xlo, float xhi, float ylo, float yhi, float zlo, float zhi, float t_min,
                        float t_max, float &enter) {
+#if RTC_NODE_CH
+  /* (xlo, xhi) etc. are (centre, half extent): distance of the centre plane, minus / plus the half extent's */
+  const float xc = fmaf(xlo, s.inv.x, -s.oi.x), yc = fmaf(ylo, s.inv.y, -s.oi.y), zc = fmaf(zlo, s.inv.z, -s.oi.z);
+  enter = fmaxf(fmaxf(fmaf(-xhi, s.ainv.x, xc), fmaf(-yhi, s.ainv.y, yc)), fmaxf(fmaf(-zhi, s.ainv.z, zc), t_min));
+  float leave = fminf(fminf(fmaf(xhi, s.ainv.x, xc), fmaf(yhi, s.ainv.y, yc)), fminf(fmaf(zhi, s.ainv.z, zc), t_max));
+#else
   float x0 = fmaf(xlo, s.inv.x, -s.oi.x), x1 = fmaf(xhi, s.inv.x, -s.oi.x);
   float y0 = fmaf(ylo, s.inv.y, -s.oi.y), y1 = fmaf(yhi, s.inv.y, -s.oi.y);
   float z0 = fmaf(zlo, s.inv.z, -s.oi.z), z1 = fmaf(zhi, s.inv.z, -s.oi.z);
   enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_min));
   float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+#endif
   /* NONNEG: the caller's t_min is >= 0, so a negative exit distance is a miss whatever the slack does to it and
    * one FMA serves (leave * (1 + 6e-7) only widens a non-negative exit).  6e-7 relative: the two axes that meet in
    * the comparison each carry inv (1.2e-7) and the FMA's rounding (6e-8), and so does the entry side. */
