@@ -221,6 +221,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   v.lights_root = desc->lights_root;
   v.world_root = built.world_root;
   v.n_media = (uint32_t)built.media.size();
+  v.n_perlins = desc->n_perlins;
   if (rc == RT_OK) {
     cudaError_t err = dev_alloc((void **)&s->counters, sizeof(RenderCounters));
     for (int k = 0; k < 4 && err == cudaSuccess; k++)

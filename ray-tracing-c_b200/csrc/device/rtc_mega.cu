@@ -99,8 +99,9 @@ RTC_DEV Ray camera_ray(const Frame &f, int pi, int pj, Rng &rng) {
 
 /* One step of Camera_ray_color (raytracing.c:39-72) for a path whose closest hit is `th`: adds what the hit emits,
  * scatters, updates the throughput.  Returns true when the path ended (its radiance L is final). */
+template <bool DEFER>
 RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th, Ray &ray, V3 &beta, V3 &L, int &depth,
-                           Rng &rng, unsigned &n_pdf) {
+                           Rng &rng, unsigned &n_pdf, PendingTex &pend) {
   if (th.prim == PRIM_NONE) {
     L = v_add(L, v_mul(beta, f.background));
     return true;
@@ -114,7 +115,7 @@ RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th,
     L = v_add(L, v_mul(beta, material_emit<false>(sc, rec)));
     return true;
   }
-  if (!material_scatter<false>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng))
+  if (!material_scatter<false, DEFER>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng, pend))
     return true;
   if (!skip_pdf && f.use_lights) { /* Book-3 mixture (raytracing.c:60-71) */
     if (rng_f32(rng) < f.prob)
@@ -235,7 +236,9 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     /* ---- phase 3: shade.  The radiance of a path stays 0 until the step that ends it (emission or background),
      * so it is not part of the state a lane carries through the walk. */
     V3 L = v3(0, 0, 0);
-    if (alive && shade_segment(sc, f, th, ray, beta, L, depth, rng, n_pdf)) {
+    PendingTex pend;
+    pend.tex = RT_NONE;
+    if (alive && shade_segment<true>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
       alive = false;
       s++;
       if (has_nan3(L)) {
@@ -246,6 +249,10 @@ __global__ void __launch_bounds__(BLOCK, MINB)
         sum = v_add(sum, L);
       }
     }
+    /* Perlin albedos owed by this trip's hits: evaluated by the whole warp, one lookup after the other (the point is the
+     * scattered ray's origin; a path that ended at max_depth owes one too, its throughput is not used again) */
+    if (sc.n_perlins)
+      perlin_settle_warp(sc, pend.tex, ray.o, beta);
   }
   /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
   flush_counters(job, n_segments, n_pdf, n_samples, n_nan);
@@ -413,6 +420,8 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
     for (int k = 0; k < NV; k++) {
       const int v = k * 32 + (int)lane;
       uint32_t meta = S.u(F_META, v);
+      PendingTex pend;
+      pend.tex = RT_NONE;
       if (meta & META_ALIVE) {
         Ray ray;
         ray.o = S.v3f(F_OX, v), ray.d = S.v3f(F_DX, v);
@@ -425,7 +434,8 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
         int depth = (int)(meta & 0xffffu);
         if (sc.n_media)
           trace_media<false>(sc, ray, 1e-3f, th, rng);
-        if (shade_segment(sc, f, th, ray, beta, L, depth, rng, n_pdf)) {
+        if (shade_segment<true>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
+          pend.tex = RT_NONE; /* the path ended: its throughput is not used again */
           meta &= ~META_ALIVE;
           S.u(F_S, v) += 1u;
           bool add = true;
@@ -443,6 +453,12 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
         }
         S.u(F_RNG_LO, v) = (uint32_t)rng.state, S.u(F_RNG_HI, v) = (uint32_t)(rng.state >> 32);
         S.u(F_META, v) = meta;
+      }
+      if (sc.n_perlins) { /* Perlin albedos owed by this slot's hits, evaluated by the whole warp */
+        V3 beta = S.v3f(F_BX, v);
+        perlin_settle_warp(sc, pend.tex, S.v3f(F_OX, v), beta);
+        if (pend.tex != RT_NONE)
+          S.put(F_BX, v, beta);
       }
     }
     __syncwarp();

@@ -99,6 +99,7 @@ struct DScene {
   const ChainOp *ops;
   const MMedium *media;
   uint32_t world_root, n_media;
+  uint32_t n_perlins; /* 0: no Perlin texture in the scene (the megakernel skips the warp-wide lookups) */
 };
 
 /* material.h:10-18 plus the id of the node that produced the hit */

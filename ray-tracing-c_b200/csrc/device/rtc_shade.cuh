@@ -185,6 +185,80 @@ template <bool EXACT> RTC_DEV V3 texture_value(const DScene &sc, uint32_t id, fl
   return texture_value_slow<EXACT>(sc, id, u, v, p);
 }
 
+/* A Perlin lookup a lane owes: the megakernel evaluates it later, with the whole warp (perlin_value_warp). */
+struct PendingTex {
+  uint32_t tex; /* RT_NONE: nothing pending.  The point is not kept: it is the hit point, i.e. the origin of the
+                   scattered ray, which the caller holds anyway */
+};
+/* texture_value for an ALBEDO (a factor of the path throughput): a Perlin texture is not evaluated here -- 7 octaves x
+ * 8 lattice corners on the one or two lanes of a warp that hit the marble sphere (ncu, Book 2 final: 8.4 % of all
+ * warp instructions at 1.9 active lanes) -- but handed back as pending, with white as the factor for now. */
+template <bool EXACT, bool DEFER>
+RTC_DEV V3 albedo_value(const DScene &sc, uint32_t id, float u, float v, V3 p, PendingTex &pend) {
+  const rt_texture *t = &sc.textures[id];
+  const uint32_t kind = __ldg(&t->kind);
+  if (kind == RT_TEX_SOLID)
+    return v3(__ldg(&t->color[0]), __ldg(&t->color[1]), __ldg(&t->color[2]));
+  if (DEFER && kind == RT_TEX_PERLIN) {
+    pend.tex = id;
+    return v3(1, 1, 1);
+  }
+  return texture_value_slow<EXACT>(sc, id, u, v, p);
+}
+
+/* Perlin_value (texture.c:47-52) for the lanes of a warp that owe one (`pending`, at the point `at`), computed by the
+ * WHOLE warp: four lookups per pass, eight lanes each, lane = octave.  Every lane evaluates one octave's noise with the
+ * reference's own corner order (perlin_noise above); the octaves of a lookup are then added by a butterfly over its
+ * eight lanes instead of one after the other -- a fixed order, whatever the warp's population, so renders stay
+ * bit-reproducible; against the sequential sum the difference is in the last bits (the megakernel's shading is
+ * judged by RMSE; the exact kernel keeps the sequential form).  All 32 lanes must call it.  Multiplies the
+ * throughput `beta` of each owing lane by its texture value. */
+static __device__ __noinline__ void perlin_settle_warp(const DScene &sc, uint32_t tex_owed, V3 at, V3 &beta) {
+  const unsigned lane = threadIdx.x & 31u, group = lane >> 3, oct0 = lane & 7u;
+  unsigned m = __ballot_sync(0xffffffffu, tex_owed != RT_NONE);
+  while (m) {
+    /* this pass serves the four lowest owing lanes; group g takes the g-th of them */
+    unsigned rest = m;
+    int src = -1;
+#pragma unroll
+    for (unsigned g = 0; g < 4; g++) {
+      const int b = rest ? __ffs(rest) - 1 : -1;
+      rest &= rest - 1u;
+      if (g == group)
+        src = b;
+    }
+    const int from = src < 0 ? 0 : src;
+    const uint32_t tex = __shfl_sync(0xffffffffu, tex_owed, from);
+    V3 p;
+    p.x = __shfl_sync(0xffffffffu, at.x, from);
+    p.y = __shfl_sync(0xffffffffu, at.y, from);
+    p.z = __shfl_sync(0xffffffffu, at.z, from);
+    float partial = 0.0f, qz = 0.0f;
+    if (src >= 0) {
+      const rt_texture *t = &sc.textures[tex];
+      const rt_perlin *pl = &sc.perlins[__ldg(&t->a)];
+      const int depth = (int)__ldg(&t->b);
+      const V3 q = v_scale(p, __ldg(&t->scale));
+      qz = q.z;
+      for (int oct = (int)oct0; oct < depth; oct += 8) {
+        const float up = __int_as_float((127 + oct) << 23), down = __int_as_float((127 - oct) << 23); /* 2^oct, 2^-oct */
+        partial += down * perlin_noise(pl, v_scale(q, up));
+      }
+    }
+    partial += __shfl_xor_sync(0xffffffffu, partial, 1);
+    partial += __shfl_xor_sync(0xffffffffu, partial, 2);
+    partial += __shfl_xor_sync(0xffffffffu, partial, 4);
+    const float value = 0.5f * (1.0f + __sinf(qz + 10.0f * fabsf(partial)));
+    /* an owing lane of rank r < 4 among the owing lanes was served by group r */
+    const unsigned rank = __popc(m & ((1u << lane) - 1u));
+    const float mine = __shfl_sync(0xffffffffu, value, (rank & 3u) << 3);
+    if (tex_owed != RT_NONE && rank < 4u) {
+      beta = v_scale(beta, mine);
+      tex_owed = RT_NONE;
+    }
+    m = rest;
+  }
+}
 /* does evaluating this texture read (u, v)?  (lets the fast kernels skip atan2f/acosf on spheres) */
 RTC_DEV bool texture_needs_uv(const DScene &sc, uint32_t id) {
   if (id == RT_NONE)
@@ -200,9 +274,9 @@ RTC_DEV V3 reflect(V3 incident, V3 normal) { /* material.c:45-47 */
 }
 
 /* material.c:103-120.  Returns false when the material does not scatter. */
-template <bool EXACT>
+template <bool EXACT, bool DEFER>
 RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_out, V3 &albedo, bool &skip_pdf,
-                              Rng &g) {
+                              Rng &g, PendingTex &pend) {
   const rt_material *m = &sc.materials[rec.material];
   uint32_t tag = __ldg(&m->tag);
   switch (tag) {
@@ -216,14 +290,14 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
     float sr2 = f_sqrt(r2);
     V3 local = v3(cs * sr2, sn * sr2, f_sqrt(1.0f - r2));
     r_out = basis_local(b, local);
-    albedo = texture_value<EXACT>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p);
+    albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = false;
     return true;
   }
   case RT_MAT_METAL: { /* material.c:48-58: three draws per try even when fuzz == 0 */
     V3 mirrored = reflect(v_unit(r_in), rec.n);
     r_out = v_add(mirrored, v_scale(rng_unit_vector(g), __ldg(&m->param)));
-    albedo = texture_value<EXACT>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p);
+    albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = true;
     if (v_dot(r_out, rec.n) < 0.0f)
       r_out = mirrored;
@@ -252,13 +326,21 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
   }
   case RT_MAT_ISOTROPIC: /* material.c:93-98 */
     r_out = rng_unit_vector(g);
-    albedo = texture_value<EXACT>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p);
+    albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = false;
     return true;
   default: /* SURFACE_NORMAL, DIFFUSE_LIGHT */
     skip_pdf = true;
     return false;
   }
+}
+
+template <bool EXACT>
+RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_out, V3 &albedo, bool &skip_pdf,
+                              Rng &g) {
+  PendingTex none;
+  none.tex = RT_NONE;
+  return material_scatter<EXACT, false>(sc, rec, r_in, r_out, albedo, skip_pdf, g, none);
 }
 
 RTC_DEV float material_scatter_pdf(const DScene &sc, uint32_t material, V3 normal, V3 r_out) { /* material.c:122-131 */
