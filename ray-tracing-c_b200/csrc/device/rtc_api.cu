@@ -189,7 +189,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   DeviceGuard guard(device);
   s->mega_ok = built.mega_supported;
   s->mega_why = built.mega_why;
-  if (s->mega_ok && built.max_stack + 1 > TRACE_STACK) {
+  if (s->mega_ok && built.max_stack + 2 > TRACE_STACK) {
     s->mega_ok = false;
     s->mega_why = "rebuilt BVH deeper than the traversal stack";
   }
@@ -256,7 +256,7 @@ extern "C" int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info) 
   info->graph_frames = (uint32_t)b.graph_frames, info->graph_rays = (uint32_t)b.graph_rays;
   info->graph_recs = (uint32_t)b.graph_recs;
   info->light_nesting = b.light_nesting;
-  info->mega_supported = b.mega_supported && b.max_stack + 1 <= TRACE_STACK;
+  info->mega_supported = b.mega_supported && b.max_stack + 2 <= TRACE_STACK;
   info->device_bytes = sizeof(rt_node) * desc->n_nodes + 4ull * desc->n_children + sizeof(rt_sphere) * desc->n_spheres +
                        sizeof(rt_quad) * desc->n_quads + sizeof(rt_material) * desc->n_materials +
                        sizeof(rt_texture) * desc->n_textures + sizeof(rt_perlin) * desc->n_perlins +

@@ -278,13 +278,14 @@ struct Walker {
   /* The ray itself and t_min are not kept here: the caller passes them to every leaf step (`outer` is a callable
    * returning the group-frame ray -- a register copy, or a reload from wherever the caller parked it). */
   RTC_DEV void begin(uint32_t root, const Ray &ray, float tmax) {
-    sp = 0, d_len2 = sv_len2(ray.d), slab = slab_setup(ray);
+    stack[0] = REF_EMPTY, sp = 1; /* the bottom entry ends the walk: pop() needs no emptiness test */
+    d_len2 = sv_len2(ray.d), slab = slab_setup(ray);
     cur = root, best_node = 0;
     best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
   }
   RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
   RTC_DEV bool done() const { return cur == REF_EMPTY; }
-  RTC_DEV uint32_t pop() { return sp == 0 ? REF_EMPTY : stack[--sp]; }
+  RTC_DEV uint32_t pop() { return stack[--sp]; } /* never called once done(): the bottom entry is REF_EMPTY */
 
   /* one inner node: both children's boxes, nearer child first, the other one pushed */
   template <bool NONNEG> RTC_DEV void visit(const DScene &sc, float t_min) {
@@ -341,20 +342,21 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
   uint32_t parked = REF_EMPTY;
   const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
   const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
+  if (!w.at_inner() && !w.done()) { /* the leaf the last round's pop left behind */
+    parked = w.cur;
+    w.cur = w.pop();
+  }
   for (;;) {
     const bool in = w.at_inner();
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
     if (in) {
       w.visit<NONNEG>(sc, t_min);
-    } else if (parked == REF_EMPTY && !w.done()) {
-      parked = w.cur;
-      w.cur = w.pop();
+      if (parked == REF_EMPTY && !w.at_inner() && !w.done()) { /* parking is part of the visit: no branch of its own */
+        parked = w.cur;
+        w.cur = w.pop();
+      }
     }
-  }
-  if (parked == REF_EMPTY && !w.at_inner() && !w.done()) {
-    parked = w.cur;
-    w.cur = w.pop();
   }
   if (parked != REF_EMPTY)
     w.leaf_test(sc, parked, t_min, outer);
