@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       wk.begin(alive ? sc.world_root : REF_EMPTY, ray, RTC_INF);
       auto outer = [&]() { return ray; };
       while (__any_sync(0xffffffffu, !wk.done()))
-        walk_round_sync<true, RTC_POSTPONE && !LOCKSTEP>(sc, wk, 1e-3f, outer, plan.thr8);
+        walk_round_sync<true, (RTC_POSTPONE == 1 && BLOCK <= 256) || RTC_POSTPONE == 2>(sc, wk, 1e-3f, outer, plan.thr8);
       th = wk.best;
     }
     if (alive) {

@@ -36,7 +36,7 @@
 #define RTC_MEDIA_FAST 1
 #endif
 #ifndef RTC_POSTPONE
-#define RTC_POSTPONE 1 /* the free-running megakernel parks the first leaf of a round and keeps descending */
+#define RTC_POSTPONE 1 /* 1: kernels of <= 256 threads park the first leaf of a round and keep descending; 2: all; 0: none */
 #endif
 #ifndef RTC_SLAB_ONE_FMA
 #define RTC_SLAB_ONE_FMA 1
@@ -337,8 +337,9 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
   /* PARK (speculative traversal): a lane that reaches a leaf parks it (one slot) and keeps descending towards its next
    * leaf while the loop runs, instead of idling until the vote ends the loop; the leaf phase tests the parked leaf.
    * The parked leaf has not shrunk t_max yet, so the descent after it can visit nodes the leaf would have culled:
-   * measured +3 % on the sphere scenes (Book 1), -2..-4 % on Cornell and Book 2 final, so only the free-running
-   * kernel (sphere-only scenes) uses it. */
+   * measured +3 % on the sphere scenes (Book 1) and on Cornell, -4 % on Book 2 final (media, quads, spheres and a
+   * marble texture: the extra visits cost more than the idle lanes there), so the kernels of up to 256 threads per
+   * CTA use it and the 512-thread lockstep kernel of the media scenes does not. */
   uint32_t parked = REF_EMPTY;
   const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
   const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
