@@ -297,15 +297,17 @@ struct Walker {
     float e0, e1;
     const bool h0 = slab_test<NONNEG>(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t, e0);
     const bool h1 = slab_test<NONNEG>(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t, e1);
+    /* three short independent steps (not an if / else-if chain): ptxas predicates them, the lanes of a warp do not
+     * split three ways at every node */
+    uint32_t next = h0 ? ch.x : ch.y;
     if (h0 && h1) {
       const bool swap = e1 < e0;
+      next = swap ? ch.y : ch.x;
       stack[sp++] = swap ? ch.x : ch.y;
-      cur = swap ? ch.y : ch.x;
-    } else if (h0 || h1) {
-      cur = h0 ? ch.x : ch.y;
-    } else {
-      cur = pop();
     }
+    if (!(h0 || h1))
+      next = pop();
+    cur = next;
   }
   /* one leaf: the primitive is tested in its own frame */
   template <class Outer> RTC_DEV void leaf_test(const DScene &sc, uint32_t ref, float t_min, Outer outer) {
