@@ -46,6 +46,7 @@ struct MegaPlan {
   int nv;                /* paths per lane: 0 = register kernel, else the warp-ray-queue kernel (rtc_mega.cu) */
   int variant;           /* index into rtc_mega.cu's table of built kernels */
   int thr8;              /* node loop runs while >= thr8/8 of the busy lanes want it (walk_round_sync) */
+  int resume8;           /* RESUME kernels: a trip's traversal ends once fewer than resume8/8 of its walkers remain */
   int chunk;             /* samples per work item */
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */

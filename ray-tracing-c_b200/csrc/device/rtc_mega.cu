@@ -27,6 +27,7 @@
 
 #define MEGA_BLOCK 128
 #define MEGA_THR8_DEFAULT 2 /* measured: see DESIGN.md */
+#define MEGA_RESUME8_DEFAULT 1 /* measured on Book 2 final: 1 +1.7 %, 2 +0.6 %, 3 -3 %, 4 -7 % */
 
 RTC_DEV bool has_nan3(V3 a) { return a.x != a.x || a.y != a.y || a.z != a.z; }
 
@@ -157,7 +158,12 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * the phases, so that all warps of a (large) CTA execute the same phase at the same time: on scenes that use every
  * code path (Book 2 final) the kernel is instruction-cache bound, and one phase's code fits the cache where the whole
  * loop body does not. */
-template <int MINB, int BLOCK, bool LOCKSTEP>
+/* RESUME: a trip's traversal does not wait for its longest rays.  Once fewer than plan.resume8/8 of the lanes that
+ * entered it are still walking it ends; the finished lanes shade, regenerate and start their next ray, the stragglers
+ * keep their walk (cursor, stack pointer, best hit: six registers; the stack is already per-thread local memory) and
+ * carry on in the next trip.  Pays where ray lengths spread widely (Book 2 final: a few rays cross the box field or
+ * the sphere cluster while most leave after a handful of nodes). */
+template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME>
 __global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
@@ -172,6 +178,11 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   V3 beta = v3(1, 1, 1), sum = v3(0, 0, 0);
   int pi = 0, pj = 0, s = 0, depth = 0, chunk_id = 0;
   bool have_item = false, alive = false;
+  /* the traversal state outlives a trip only in the RESUME kernels */
+  uint32_t stack[TRACE_STACK];
+  Walker wk;
+  wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 1;
+  bool walking = false;
 
   bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
   for (;;) {
@@ -214,16 +225,29 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     /* ---- phase 2: one closest-hit query for every live lane, entered together */
     TraceHit th;
     {
-      uint32_t stack[TRACE_STACK];
-      Walker wk;
-      wk.stack = stack;
-      wk.begin(alive ? sc.world_root : REF_EMPTY, ray, RTC_INF);
+      constexpr bool PARK = (RTC_POSTPONE == 1 && BLOCK <= 256) || RTC_POSTPONE == 2;
+      if (RESUME && walking)
+        wk.resume(ray);
+      else
+        wk.begin(alive ? sc.world_root : REF_EMPTY, ray, RTC_INF);
       auto outer = [&]() { return ray; };
-      while (__any_sync(0xffffffffu, !wk.done()))
-        walk_round_sync<true, (RTC_POSTPONE == 1 && BLOCK <= 256) || RTC_POSTPONE == 2>(sc, wk, 1e-3f, outer, plan.thr8);
+      if (RESUME) {
+        const int entered = __popc(__ballot_sync(0xffffffffu, !wk.done()));
+        const int stop_below = (entered * plan.resume8 + 7) >> 3;
+        for (;;) {
+          const int left = __popc(__ballot_sync(0xffffffffu, !wk.done()));
+          if (left == 0 || left < stop_below)
+            break;
+          walk_round_sync<true, PARK>(sc, wk, 1e-3f, outer, plan.thr8);
+        }
+        walking = !wk.done();
+      } else {
+        while (__any_sync(0xffffffffu, !wk.done()))
+          walk_round_sync<true, PARK>(sc, wk, 1e-3f, outer, plan.thr8);
+      }
       th = wk.best;
     }
-    if (alive) {
+    if (alive && !(RESUME && walking)) {
       n_segments++;
       if (sc.n_media)
         trace_media<false>(sc, ray, 1e-3f, th, rng);
@@ -238,7 +262,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     V3 L = v3(0, 0, 0);
     PendingTex pend;
     pend.tex = RT_NONE;
-    if (alive && shade_segment<true>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
+    if (alive && !(RESUME && walking) && shade_segment<true>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
       alive = false;
       s++;
       if (has_nan3(L)) {
@@ -490,12 +514,16 @@ struct MegaVariant {
 static const MegaVariant mega_variants[] = {
     {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK}, /* first entry of an nv = its default */
     {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
-    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
-    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false>, 0, MEGA_BLOCK},
-    {-1, 4, mega_render_kernel<4, 256, true>, 0, 256},
-    {-1, 2, mega_render_kernel<2, 512, true>, 0, 512},
-    {-1, 1, mega_render_kernel<1, 1024, true>, 0, 1024},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
+    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
+    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
+    {-1, 4, mega_render_kernel<4, 256, true, false>, 0, 256},
+    {-1, 2, mega_render_kernel<2, 512, true, false>, 0, 512},
+    {-1, 1, mega_render_kernel<1, 1024, true, false>, 0, 1024},
+    /* nv = -2: lockstep CTAs whose trips do not wait for their longest rays (RESUME); nv = -3: the same, free-running */
+    {-2, 2, mega_render_kernel<2, 512, true, true>, 0, 512},
+    {-2, 4, mega_render_kernel<4, 256, true, true>, 0, 256},
+    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true>, 0, MEGA_BLOCK},
 };
 static int env_int(const char *name, int fallback) {
   const char *v = getenv(name);
@@ -503,14 +531,15 @@ static int env_int(const char *name, int fallback) {
 }
 /* Which kernel renders a scene.  Default, from measurements on the eight reference scenes: free-running
  * 128-thread CTAs for sphere-only scenes; lockstep CTAs of 256 threads once the scene has quads (Cornell +5 %, the
- * quad scene +12 %), of 512 threads once it has media (Book 2 final +34 %: instruction cache).  RT_MEGA_NV (paths per
- * lane: 0 = free-running register kernel, -1 = lockstep, 2/4 = warp ray queue) and RT_MEGA_MINB (CTAs per SM the
+ * quad scene +12 %), of 512 threads once it has media (Book 2 final +34 %: instruction cache; there also RESUME,
+ * +1.7 %).  RT_MEGA_NV (paths per lane: 0 = free-running register kernel, -1 = lockstep, -2 = lockstep + RESUME,
+ * -3 = free-running + RESUME, 2/4 = warp ray queue) and RT_MEGA_MINB (CTAs per SM the
  * registers must allow) override; a combination that is not built falls back to the nv's first entry. */
 static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class) {
   int nv = env_int("RT_MEGA_NV", -99), minb = env_int("RT_MEGA_MINB", 0);
   if (nv == -99) {
-    nv = scene_class == MEGA_SCENE_SPHERES ? 0 : -1;
-    if (minb == 0 && nv == -1)
+    nv = scene_class == MEGA_SCENE_SPHERES ? 0 : scene_class == MEGA_SCENE_MEDIA ? -2 : -1;
+    if (minb == 0 && nv < 0)
       minb = scene_class == MEGA_SCENE_MEDIA ? 2 : 4;
   }
   int want_nv = nv;
@@ -581,6 +610,8 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   {
     int t = env_int("RT_MEGA_THR8", MEGA_THR8_DEFAULT); /* see walk_round_sync */
     plan->thr8 = t < 0 ? 0 : t > 8 ? 8 : t;
+    int r = env_int("RT_MEGA_RESUME8", MEGA_RESUME8_DEFAULT); /* see mega_render_kernel, RESUME */
+    plan->resume8 = r < 0 ? 0 : r > 8 ? 8 : r;
   }
   plan->nv = var->nv;
   plan->minb = var->minb;

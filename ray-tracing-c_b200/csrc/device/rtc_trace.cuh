@@ -294,6 +294,8 @@ struct Walker {
     cur = root, best_node = 0;
     best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
   }
+  /* a walk that was suspended (cur, sp, best kept; the stack is the caller's array): the per-ray constants again */
+  RTC_DEV void resume(const Ray &ray) { d_len2 = sv_len2(ray.d), slab = slab_setup(ray); }
   RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
   RTC_DEV bool done() const { return cur == REF_EMPTY; }
   RTC_DEV uint32_t pop() { return stack[--sp]; } /* never called once done(): the bottom entry is REF_EMPTY */
