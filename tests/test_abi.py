@@ -159,3 +159,21 @@ def test_cli_matches_reference_argument_quirk(rtc):
         assert proc.returncode != 0
         assert "render failed" in proc.stderr
         assert not (Path(tmp) / "output.tiff").exists()
+
+
+def test_flattened_instances_are_counted_and_capped(rtc, scene_factory):
+    """Translate/RotateY chains do not become nodes of the rebuilt tree: their primitives join the group's one BVH
+    tagged with the chain (8 bits).  60 chains: supported, 60 instances of 2 ops each; 300 chains: the throughput
+    kernels refuse (RT_ERR_UNSUPPORTED at render time), the description stays valid for the exact kernel."""
+    from synth_scenes import instanced_scene
+
+    _, base = scene_factory(1, 48, 4)
+    d60 = instanced_scene(rtc, base, 60)
+    info = rtc.inspect(d60)
+    assert info["mega_supported"] == 1
+    assert info["instances"] == 60 and info["chain_ops"] == 120
+    assert info["spheres"] + info["quads"] == 60 + 6 + 1
+    assert info["bvh_nodes"] == info["spheres"] + info["quads"] - 1  # one primitive per leaf, one tree
+    d300 = instanced_scene(rtc, base, 300)
+    info = rtc.inspect(d300)
+    assert info["mega_supported"] == 0 and info["instances"] >= 255

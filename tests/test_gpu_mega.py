@@ -291,3 +291,32 @@ def test_unknown_kernel_is_refused(rtc, gpu_scene):
     with pytest.raises(rtc.lib.RtError) as err:
         scene.render(sess.camera, rtc.make_opts(kernel=9))
     assert err.value.status in (rtc.abi.RT_ERR_UNSUPPORTED, rtc.abi.RT_ERR_INVALID)
+
+
+@pytest.mark.parametrize("n_instances,with_quads", [(60, True), (200, False)])
+def test_many_flattened_instances_hit_parity(rtc, scene_factory, n_instances, with_quads):
+    """Dozens of Translate(RotateY(primitive)) chains with arbitrary angles and offsets (the reference's scenes have
+    at most two): the rebuilt tree bounds every primitive in the world frame and tests it in its own -- hit distances
+    and ids must still be the exact kernel's (= the reference's order of operations) bit for bit, from outside and
+    from points inside the cloud."""
+    from synth_scenes import instanced_scene
+
+    _, base = scene_factory(1, 48, 4)
+    desc = instanced_scene(rtc, base, n_instances, seed=11 + n_instances, with_quads=with_quads)
+    scene = rtc.Scene(desc)
+    try:
+        rng = np.random.default_rng(5)
+        n = 60000
+        o = np.concatenate([np.tile(np.array([[0, 3, 40]], np.float32), (n // 2, 1)),
+                            rng.uniform(-15, 15, (n - n // 2, 3)).astype(np.float32)])
+        target = rng.uniform(-16, 16, (n, 3)).astype(np.float32)
+        d = (target - o).astype(np.float32)
+        ref = scene.hit_batch(o, d, 1e-3, np.inf, kernel="exact")
+        got = scene.hit_batch(o, d, 1e-3, np.inf, kernel="mega")
+        assert np.isfinite(ref["t"]).mean() > 0.2
+        assert same_bits(got["t"], ref["t"]).all()
+        assert (got["node"] == ref["node"]).all()
+        hit = np.isfinite(ref["t"])
+        assert same_bits(got["p"][hit], ref["p"][hit]).all() and same_bits(got["normal"][hit], ref["normal"][hit]).all()
+    finally:
+        scene.close()
