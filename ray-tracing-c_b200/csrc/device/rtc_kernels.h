@@ -47,6 +47,7 @@ struct MegaPlan {
   int variant;           /* index into rtc_mega.cu's table of built kernels */
   int thr8;              /* node loop runs while >= thr8/8 of the busy lanes want it (walk_round_sync) */
   int resume8;           /* RESUME kernels: a trip's traversal ends once fewer than resume8/8 of its walkers remain */
+  int cta8;              /* lockstep RESUME kernels: ... or once cta8/8 of the CTA's warps have finished theirs (0: off) */
   int chunk;             /* samples per work item */
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */

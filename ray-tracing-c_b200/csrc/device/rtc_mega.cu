@@ -27,6 +27,7 @@
 
 #define MEGA_BLOCK 128
 #define MEGA_THR8_DEFAULT 2 /* measured: see DESIGN.md */
+#define MEGA_CTA8_DEFAULT 3 /* measured on Book 2 final: 3 +6 %, 4 +5.6 %, 6 +3.3 %, 7 +1.9 % (0 = off) */
 #define MEGA_RESUME8_DEFAULT 1 /* measured on Book 2 final: 1 +1.7 %, 2 +0.6 %, 3 -3 %, 4 -7 % */
 
 RTC_DEV bool has_nan3(V3 a) { return a.x != a.x || a.y != a.y || a.z != a.z; }
@@ -162,7 +163,11 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * entered it are still walking it ends; the finished lanes shade, regenerate and start their next ray, the stragglers
  * keep their walk (cursor, stack pointer, best hit: six registers; the stack is already per-thread local memory) and
  * carry on in the next trip.  Pays where ray lengths spread widely (Book 2 final: a few rays cross the box field or
- * the sphere cluster while most leave after a handful of nodes). */
+ * the sphere cluster while most leave after a handful of nodes).
+ * In the LOCKSTEP kernels the same machinery bounds the wait at the CTA barrier (ncu: 3.5 of the 14 cycles between two
+ * issues of a warp there): once plan.cta8/8 of the CTA's warps have finished the trip's traversal, the others suspend
+ * theirs too (after at least one round, so every trip makes progress; warps without work do not count, so nobody is
+ * suspended when few warps have work left). */
 template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME>
 __global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
@@ -184,8 +189,19 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 1;
   bool walking = false;
 
+  /* lockstep RESUME kernels: how many warps of the CTA have finished this trip's traversal (one counter per trip
+   * parity; the idle one is cleared between the barriers) */
+  __shared__ int warps_finished[2];
+  if (LOCKSTEP && RESUME) {
+    if (threadIdx.x < 2)
+      warps_finished[threadIdx.x] = 0;
+    __syncthreads();
+  }
+  const int stop_warps = (LOCKSTEP && RESUME && plan.cta8 > 0) ? max(1, ((BLOCK / 32) * plan.cta8) >> 3) : 0x7fffffff;
+  unsigned trip = 0;
+
   bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
-  for (;;) {
+  for (;; trip++) {
     /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
     if (!alive && !done) {
       if (have_item && s == min(job.sample_begin + (chunk_id + 1) * plan.chunk, job.sample_begin + job.sample_count)) {
@@ -234,12 +250,25 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       if (RESUME) {
         const int entered = __popc(__ballot_sync(0xffffffffu, !wk.done()));
         const int stop_below = (entered * plan.resume8 + 7) >> 3;
-        for (;;) {
+        volatile int *finished = &warps_finished[trip & 1u];
+        if (LOCKSTEP && threadIdx.x == 0)
+          warps_finished[(trip & 1u) ^ 1u] = 0; /* last used before the previous trip's second barrier */
+        bool natural = true;
+        for (int round = 0;; round++) {
           const int left = __popc(__ballot_sync(0xffffffffu, !wk.done()));
           if (left == 0 || left < stop_below)
             break;
+          /* most of the CTA's working warps wait at the barrier: suspend this warp's walks (never before its first
+           * round of the trip, so every trip makes progress) */
+          if (LOCKSTEP && round > 0 && *finished >= stop_warps) {
+            natural = false;
+            break;
+          }
           walk_round_sync<true, PARK>(sc, wk, 1e-3f, outer, plan.thr8);
         }
+        /* a warp that had nothing to trace does not count: when few warps have work left nobody is suspended */
+        if (LOCKSTEP && natural && entered > 0 && (threadIdx.x & 31) == 0)
+          atomicAdd(&warps_finished[trip & 1u], 1);
         walking = !wk.done();
       } else {
         while (__any_sync(0xffffffffu, !wk.done()))
@@ -612,6 +641,8 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
     plan->thr8 = t < 0 ? 0 : t > 8 ? 8 : t;
     int r = env_int("RT_MEGA_RESUME8", MEGA_RESUME8_DEFAULT); /* see mega_render_kernel, RESUME */
     plan->resume8 = r < 0 ? 0 : r > 8 ? 8 : r;
+    int c = env_int("RT_MEGA_CTA8", MEGA_CTA8_DEFAULT);
+    plan->cta8 = c < 0 ? 0 : c > 8 ? 8 : c;
   }
   plan->nv = var->nv;
   plan->minb = var->minb;

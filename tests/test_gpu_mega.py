@@ -207,12 +207,15 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
     variants = [("0", "6", "2"), ("0", "4", "0"), ("-1", "4", "2"), ("-1", "2", "2"), ("-1", "1", "4"),
                 ("2", "6", "2"), ("4", "4", "0"),
                 # RESUME kernels (a trip ends before its longest rays do; stragglers carry on in the next trip)
-                ("-2", "2", "2", "1"), ("-2", "4", "2", "3"), ("-3", "8", "2", "2"), ("-3", "8", "1", "6")]
+                # (4th: RT_MEGA_RESUME8; 5th: RT_MEGA_CTA8, the CTA-wide early end of a lockstep trip, 0 = off)
+                ("-2", "2", "2", "1"), ("-2", "2", "2", "1", "0"), ("-2", "2", "2", "2", "6"), ("-2", "4", "2", "3", "1"),
+                ("-3", "8", "2", "2"), ("-3", "8", "1", "6")]
     for nv, minb, thr8, *resume8 in variants:
         monkeypatch.setenv("RT_MEGA_NV", nv)
         monkeypatch.setenv("RT_MEGA_MINB", minb)
         monkeypatch.setenv("RT_MEGA_THR8", thr8)
         monkeypatch.setenv("RT_MEGA_RESUME8", resume8[0] if resume8 else "1")
+        monkeypatch.setenv("RT_MEGA_CTA8", resume8[1] if len(resume8) > 1 else "3")
         rgb, rad, st = scene.render(sess.camera, opts)
         assert same_bits(rad, rad_ref).all(), (nv, minb, thr8, resume8)
         assert np.array_equal(rgb, rgb_ref)
