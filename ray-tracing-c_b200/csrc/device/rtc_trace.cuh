@@ -322,6 +322,31 @@ struct Walker {
       next = pop();
     cur = next;
   }
+  /* visit() for a caller that parks leaves (walk_round_sync<PARK>): when the child the walk would continue with is a
+   * leaf and the parking slot is free, the leaf goes to the slot; if both children were hit the walk then continues
+   * with the farther child directly -- no push, no pop -- else with the next stack entry. */
+  template <bool NONNEG> RTC_DEV void visit_park(const DScene &sc, float t_min, uint32_t &parked) {
+    float4 xy0, xy1, zz;
+    uint2 ch;
+    ldg_node<NONNEG && RTC_NODE_WIDE>(sc.bnodes + cur, xy0, xy1, zz, ch);
+    float e0, e1;
+    const bool h0 = slab_test<NONNEG>(slab, xy0.x, xy0.y, xy0.z, xy0.w, zz.x, zz.y, t_min, best.t, e0);
+    const bool h1 = slab_test<NONNEG>(slab, xy1.x, xy1.y, xy1.z, xy1.w, zz.z, zz.w, t_min, best.t, e1);
+    const bool both = h0 && h1, none = !(h0 || h1);
+    const bool swap = both && e1 < e0;
+    uint32_t next = (h0 && !swap) ? ch.x : ch.y; /* the only child hit, or the nearer of the two */
+    const uint32_t far = swap ? ch.x : ch.y;
+    const bool park = parked == REF_EMPTY && !none && REF_KIND(next) != REF_INNER;
+    if (park)
+      parked = next;
+    if (both && !park)
+      stack[sp++] = far;
+    if (both && park)
+      next = far;
+    if (none || (park && !both))
+      next = pop();
+    cur = next;
+  }
   /* one leaf: the primitive is tested in its own frame */
   template <class Outer> RTC_DEV void leaf_test(const DScene &sc, uint32_t ref, float t_min, Outer outer) {
     const uint32_t tag = REF_TAG(ref);
@@ -366,13 +391,8 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
     const bool in = w.at_inner();
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
-    if (in) {
-      w.visit<NONNEG>(sc, t_min);
-      if (parked == REF_EMPTY && !w.at_inner() && !w.done()) { /* parking is part of the visit: no branch of its own */
-        parked = w.cur;
-        w.cur = w.pop();
-      }
-    }
+    if (in)
+      w.visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
   }
   if (parked != REF_EMPTY)
     w.leaf_test(sc, parked, t_min, outer);
