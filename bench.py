@@ -40,9 +40,9 @@ UNIT = "Mseg/s"
 SCENE_ID, WIDTH, SPP, DEPTH = 1, 1200, 1000, 50
 REF_FAST = ROOT / "oracle" / "_ref" / "ref_main_fast"
 # dram__bytes_read.sum + dram__bytes_write.sum of mega_render_kernel per launch, from profiles/ (ncu --set full);
-# profiles/r01h_mega_render_kernel_book1_1000spp.txt (the bench's own launch: 1200x675, 1000 spp): 24.8 MB read +
-# 5.469 GB written -- local-memory (traversal stack, spills) write-backs from L2, 23 GB/s, 0.27 % of DRAM peak
-NCU_DRAM_BYTES_PER_LAUNCH = 5.494e9
+# profiles/r01j_mega_render_kernel_book1_1000spp.txt (the bench's own launch: 1200x675, 1000 spp): 27.5 MB read +
+# 5.062 GB written -- local-memory (traversal stack, spills) write-backs from L2, 22 GB/s, 0.26 % of DRAM peak
+NCU_DRAM_BYTES_PER_LAUNCH = 5.090e9
 FALLBACK_FLOP_PER_SEGMENT = 1434.0  # scene 1; recomputed live from the oracle's counters when possible
 
 
