@@ -373,33 +373,31 @@ struct Walker {
  * early costs nothing: a lane that is still descending just carries on in the next round. */
 template <bool NONNEG, bool PARK, class Outer>
 RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer outer, int thr8) {
+  const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
+  const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
   if (PARK) {
-  /* PARK (speculative traversal): a lane that reaches a leaf parks it (one slot) and keeps descending towards its next
-   * leaf while the loop runs, instead of idling until the vote ends the loop; the leaf phase tests the parked leaf.
-   * The parked leaf has not shrunk t_max yet, so the descent after it can visit nodes the leaf would have culled:
-   * measured +3 % on the sphere scenes (Book 1) and on Cornell, -4 % on Book 2 final (media, quads, spheres and a
-   * marble texture: the extra visits cost more than the idle lanes there), so the kernels of up to 256 threads per
-   * CTA use it and the 512-thread lockstep kernel of the media scenes does not. */
-  uint32_t parked = REF_EMPTY;
-  const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
-  const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
-  if (!w.at_inner() && !w.done()) { /* the leaf the last round's pop left behind */
-    parked = w.cur;
-    w.cur = w.pop();
+    /* PARK (speculative traversal): a lane that reaches a leaf parks it (one slot) and keeps descending towards its
+     * next leaf while the loop runs, instead of idling until the vote ends the loop; the leaf phase tests the parked
+     * leaf.  The parked leaf has not shrunk t_max yet, so the descent after it can visit nodes the leaf would have
+     * culled: measured +3 % on the sphere scenes (Book 1) and on Cornell, -4 % on Book 2 final (media, quads, spheres
+     * and a marble texture: the extra visits cost more than the idle lanes there), so the kernels of up to 256 threads
+     * per CTA use it and the 512-thread lockstep kernel of the media scenes does not. */
+    uint32_t parked = REF_EMPTY;
+    if (!w.at_inner() && !w.done()) { /* the leaf the last round's pop left behind */
+      parked = w.cur;
+      w.cur = w.pop();
+    }
+    for (;;) {
+      const bool in = w.at_inner();
+      if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
+        break;
+      if (in)
+        w.visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
+    }
+    if (parked != REF_EMPTY)
+      w.leaf_test(sc, parked, t_min, outer);
+    return;
   }
-  for (;;) {
-    const bool in = w.at_inner();
-    if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
-      break;
-    if (in)
-      w.visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
-  }
-  if (parked != REF_EMPTY)
-    w.leaf_test(sc, parked, t_min, outer);
-  return;
-  }
-  const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
-  const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
   for (;;) {
     const bool in = w.at_inner();
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
