@@ -5,8 +5,9 @@
  * (/root/reference/src/hittable.c:284-323), tests ~43 boxes per segment on the Book-1 scene, never bounds its
  * Translate/RotateY instances (hittable.c:325-334,354-367) and keeps top-level items in a linear list.  For the
  * megakernel we keep the reference's PRIMITIVES and TRANSFORMS (so hit distances stay bit-identical) but rebuild
- * everything around them: one binned-SAH binary BVH per frame of reference ("group"), instances as leaves with
- * conservative world-space bounds, media evaluated after the surfaces.
+ * everything around them: ONE binned-SAH binary BVH per group (the world, or a medium's boundary) with one primitive
+ * per leaf; primitives under Translate / RotateY chains are flattened into it with tight boxes in the group's frame
+ * and a tag naming their chain; media are evaluated after the surfaces.
  */
 #ifndef RTC_BVH_H
 #define RTC_BVH_H

@@ -1,13 +1,15 @@
 /*
  * rtc_trace.cuh -- closest hit over the REBUILT structure (rtc_bvh.h): ordered traversal of a binary BVH whose
- * nodes carry both children's boxes (four 16-byte loads per visit), primitives read with 16-byte loads,
- * instances entered by transforming the ray with the reference's own operation sequence, media evaluated after
+ * nodes carry both children's boxes as (centre, half extent) (two 256-bit loads and 18 FMAs per visit), one primitive
+ * per leaf read with 16-byte loads, primitives under Translate / RotateY chains bounded in the group's frame and
+ * tested in their own (the ray is moved there with the reference's own operation sequence), media evaluated after
  * the surfaces.  Replaces HittableList_hit / BVHNode_hit / AABB_hit / Translate_hit / RotateY_hit /
  * ConstantMedium_hit (/root/reference/src/hittable.c:38-55, 74-88, 266-277, 325-423) on the throughput path.
  *
- * Hit distances come from sphere_isect / quad_isect (strict arithmetic), so they carry the reference's bits; what differs
- * from the reference is only the ORDER in which candidates are met.  Ties are resolved as the reference's visiting
- * order would (quads: the later node id wins, closed interval; spheres: open interval), see closer_quad().
+ * Hit distances come from strict arithmetic in the reference's operation order (sphere_isect_closed, leaf_intersect),
+ * so they carry the reference's bits; what differs from the reference is only the ORDER in which candidates are met.
+ * Ties are resolved as the reference's visiting order would (quads: the later node id wins, closed interval;
+ * spheres: the earlier node id wins, open interval), see leaf_intersect().
  */
 #ifndef RTC_TRACE_CUH
 #define RTC_TRACE_CUH
