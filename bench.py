@@ -275,7 +275,8 @@ def b200_arm(args):
     h, w = cam.img_height, cam.img_width
     barrier()
     e2e_ms = []
-    for it in range(-1, e2e_steps):  # iteration -1 is the untimed warm-up (first-use allocations of the pools)
+    e2e_warm = max(1, min(args.warmup, 3))
+    for it in range(-e2e_warm, e2e_steps):  # negative iterations: untimed warm-up (first-use allocations of the pools)
         barrier()
         t0 = time.perf_counter()
         if world == 1:
