@@ -73,3 +73,32 @@ def test_two_rank_sample_shards_reduce_to_the_full_render(rtc, oracle, tmp_path)
     ok, same_image = out.read_text().split()
     assert ok == "1"
     assert same_image == "1"
+
+
+def test_bench_reference_arm_contract(tmp_path):
+    """`bench.py --impl reference` (the driver's reference arm): rank 0 prints ONE JSON line with the metric of the
+    backend's own arm, `impl: reference`, a cpu_baseline describing the run and an e2e object with zero copies;
+    every other rank exits 0 without work.  Small frame: the arm times the reference's CPU code, no GPU involved."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    cmd = [sys.executable, str(root / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+           "--width", "160", "--spp", "8", "--ref-spp", "2"]
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE")}
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["unit"] == "Mseg/s" and line["higher_is_better"] is True
+    assert line["value"] > 0 and line["ms_per_step"] > 0 and line["vs_baseline"] is None
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    assert line["cpu_baseline"]["value"] == line["value"] and line["cpu_baseline"]["sample"]
+    assert line["e2e"] == {"value": line["value"], "unit": "Mseg/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    other = subprocess.run(cmd, env=dict(env, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2"), capture_output=True,
+                           text=True, timeout=300)
+    assert other.returncode == 0 and other.stdout.strip() == ""
