@@ -117,7 +117,8 @@ def main():
                 "config": name, "scene": scene_id, "image": [sess.width, sess.height], "spp_rendered": gpu_spp,
                 "spp_config": spp, "kernel": kernel, "segments": st["segments"], "kernel_ms": st["kernel_ms"],
                 "total_ms": st["total_ms"], "mseg_per_s": mseg, "seg_per_sample": st["segments"] / st["samples"],
-                "full_frame_seconds": st["total_ms"] * 1e-3 * spp / gpu_spp,
+                # kernel time scales with spp; upload, tonemap and the copies back are per frame
+                "full_frame_seconds": (st["kernel_ms"] * spp / gpu_spp + (st["total_ms"] - st["kernel_ms"])) * 1e-3,
                 "flop_per_segment_reference_traversal": flop_per_seg,
                 "algorithmic_tflops": mseg * 1e6 * flop_per_seg * 1e-12, "nan_samples": st["nan_samples"],
                 "cpu_reference": cpu,
