@@ -8,7 +8,11 @@
  * hittable.c / material.c / texture.c / raytracing.c / vec3.c / pcg32.c / utils.c as they are, and links THIS
  * repo's flatten.c so that the very same flattener runs over a graph built by the reference's constructors.
  *
- *   ref_tool render  <scene> <width> <spp> <depth> <aspect|0> <out.rgb8>   Camera_render of the reference
+ *   ref_tool render  <scene> <width> <spp> <depth> <aspect|0> <out.rgb8> <out.camera>
+ *                                                                           Camera_render of the reference; prints
+ *                                                                           `render_seconds=<s>` (monotonic clock around
+ *                                                                           Camera_render only: the scope of the
+ *                                                                           reference's own timer, src/main.c:334-338)
  *   ref_tool flatten <scene> <out.blob>                                     rt_scene_desc of the reference's graph
  *   ref_tool hits    <scene> <rays.bin> <out.bin>                           world.objects.hit() on a ray batch
  *
@@ -22,6 +26,7 @@
 #include "rtc_b200.h"
 #include <math.h>
 #include <string.h>
+#include <time.h>
 
 /* from this repo's flatten.c / image_io.c (declared by hand: rtc_host.h would redeclare the reference's types) */
 int rtc_flatten(const World *world, rt_scene_desc *out);
@@ -105,7 +110,11 @@ int main(int argc, char **argv) {
     Camera_init(&camera);
     size_t n = (size_t)camera.img_width * camera.img_height * 3;
     uint8_t *image = malloc(n);
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
     Camera_render(&camera, &world, image);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    printf("render_seconds=%.6f\n", (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec));
     FILE *f = fopen(argv[7], "wb");
     assert(f != NULL);
     fwrite(image, 1, n, f);

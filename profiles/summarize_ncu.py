@@ -4,6 +4,10 @@
     python profiles/summarize_ncu.py launches gpurun_out/launches.csv              > profiles/rNN_launches.txt
     python profiles/summarize_ncu.py kernel   gpurun_out/prof.ncu-rep [kernel-idx] > profiles/rNN_<kernel>.txt
 
+    python profiles/summarize_ncu.py json     gpurun_out/prof.ncu-rep configN <segments> <committed summary path> [idx]
+                                              -> updates profiles/ncu_summary.json (what bench.py quotes as `executed`,
+                                                 `traffic`, `issue_active`, `lanes_per_inst` for that configuration)
+
 `launches`: per-kernel totals and SHARES of a `--metrics gpu__time_duration.sum` pass (cold-cache, serialised: the
 shares are what counts).  `kernel`: the counters the north star names (warp execution efficiency, L1/L2 hit rates,
 issue rate, DRAM bytes and GB/s), registers/occupancy, the stall-reason mix, the opcode mix and the per-instruction
@@ -113,8 +117,54 @@ def kernel(report, index=0):
           ", ".join(f"{k} {100 * v / tot_i:.1f}" for k, v in ops.most_common(16)))
 
 
+def to_json(report, key, segments, source, index=0):
+    import json
+    from pathlib import Path
+
+    rows = ncu_csv(report, "raw")
+    header, units = rows[0], rows[1]
+    values = rows[2 + index]
+    col = {h: i for i, h in enumerate(header)}
+
+    def val(name, scale_units=None):
+        if name not in col:
+            return None
+        v = float(values[col[name]].replace(",", ""))
+        if scale_units:
+            v *= scale_units.get(units[col[name]], 1.0)
+        return v
+
+    byte_units = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    time_units = {"ns": 1e-6, "nsecond": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}
+    hz_units = {"hz": 1.0, "Khz": 1e3, "Mhz": 1e6, "Ghz": 1e9}
+    ms = val("gpu__time_duration.sum", time_units)
+    cycles = ms * 1e-3 * val("sm__cycles_elapsed.avg.per_second", hz_units)
+    flop = (2 * val("smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed") +
+            val("smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed") +
+            val("smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed")) * cycles
+    warp_inst = val("smsp__inst_executed.sum")
+    local = (val("smsp__inst_executed_op_local_ld.sum") or 0.0) + (val("smsp__inst_executed_op_local_st.sum") or 0.0)
+    entry = {
+        "source": source, "kernel": values[col["Kernel Name"]], "n_gpus": 1, "segments": int(segments),
+        "duration_ms": ms,
+        "dram_bytes": val("dram__bytes_read.sum", byte_units) + val("dram__bytes_write.sum", byte_units),
+        "flop_executed": flop, "warp_inst": warp_inst,
+        "lanes_per_inst": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+        "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+        "l1_hit_pct": val("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
+        "local_ld_st_pct_of_warp_inst": 100.0 * local / warp_inst if warp_inst else None,
+    }
+    path = Path(__file__).resolve().parent / "ncu_summary.json"
+    table = json.loads(path.read_text()) if path.exists() else {}
+    table[key] = entry
+    path.write_text(json.dumps(table, indent=1) + "\n")
+    print(json.dumps(entry, indent=1))
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
+    elif sys.argv[1] == "json":
+        to_json(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5], int(sys.argv[6]) if len(sys.argv) > 6 else 0)
     else:
         kernel(sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 0)

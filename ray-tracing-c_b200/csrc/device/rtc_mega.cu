@@ -184,9 +184,11 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   int pi = 0, pj = 0, s = 0, depth = 0, chunk_id = 0;
   bool have_item = false, alive = false;
   /* the traversal state outlives a trip only in the RESUME kernels */
-  uint32_t stack[TRACE_STACK];
-  Walker wk;
+  uint32_t stack[TRACE_STACK - RTC_SMEM_STACK];
+  WalkerT<RTC_SMEM_STACK> wk;
   wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 1;
+  /* dynamic shared memory: RTC_SMEM_STACK * BLOCK words (mega_variants) */
+  wk.sbase = (uint32_t)__cvta_generic_to_shared(rtc_dyn_smem + threadIdx.x), wk.sstride = 4u * BLOCK;
   bool walking = false;
 
   /* lockstep RESUME kernels: how many warps of the CTA have finished this trip's traversal (one counter per trip
@@ -260,7 +262,9 @@ __global__ void __launch_bounds__(BLOCK, MINB)
             break;
           /* most of the CTA's working warps wait at the barrier: suspend this warp's walks (never before its first
            * round of the trip, so every trip makes progress) */
-          if (LOCKSTEP && round > 0 && *finished >= stop_warps) {
+          /* (other warps add to the counter concurrently: the decision is made from ONE read, lane 0's, so that all
+           * 32 lanes leave together -- the next statement after the loop is a full-mask ballot) */
+          if (LOCKSTEP && round > 0 && __shfl_sync(0xffffffffu, *finished, 0) >= stop_warps) {
             natural = false;
             break;
           }
@@ -331,7 +335,7 @@ enum {
 #define META_ITEM (1u << 25)
 #define META_DONE (1u << 26)
 
-extern __shared__ __align__(16) uint32_t mega_smem[];
+#define mega_smem rtc_dyn_smem
 template <int NV> struct WarpSlots {
   unsigned base; /* word offset of the warp's [F_COUNT][NV][32] words (an offset, not a pointer: the accesses stay
                     plain shared-memory loads and stores) */
@@ -540,19 +544,20 @@ struct MegaVariant {
   size_t smem;
   int block;
 };
+#define STACK_SMEM(block) ((size_t)RTC_SMEM_STACK * (block) * sizeof(uint32_t)) /* WalkerT's shared-memory entries */
 static const MegaVariant mega_variants[] = {
     {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK}, /* first entry of an nv = its default */
     {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
-    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
-    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false>, 0, MEGA_BLOCK},
-    {-1, 4, mega_render_kernel<4, 256, true, false>, 0, 256},
-    {-1, 2, mega_render_kernel<2, 512, true, false>, 0, 512},
-    {-1, 1, mega_render_kernel<1, 1024, true, false>, 0, 1024},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
+    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
+    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
+    {-1, 4, mega_render_kernel<4, 256, true, false>, STACK_SMEM(256), 256},
+    {-1, 2, mega_render_kernel<2, 512, true, false>, STACK_SMEM(512), 512},
+    {-1, 1, mega_render_kernel<1, 1024, true, false>, STACK_SMEM(1024), 1024},
     /* nv = -2: lockstep CTAs whose trips do not wait for their longest rays (RESUME); nv = -3: the same, free-running */
-    {-2, 2, mega_render_kernel<2, 512, true, true>, 0, 512},
-    {-2, 4, mega_render_kernel<4, 256, true, true>, 0, 256},
-    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true>, 0, MEGA_BLOCK},
+    {-2, 2, mega_render_kernel<2, 512, true, true>, STACK_SMEM(512), 512},
+    {-2, 4, mega_render_kernel<4, 256, true, true>, STACK_SMEM(256), 256},
+    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
 };
 static int env_int(const char *name, int fallback) {
   const char *v = getenv(name);

@@ -45,6 +45,13 @@
 #endif
 
 #define TRACE_STACK 48          /* rt_scene_create refuses deeper structures for the mega/wave kernels */
+/* RTC_SMEM_STACK = K > 0: the render kernels keep the first K entries of every lane's traversal stack in SHARED memory,
+ * laid out [entry][thread] (bank = lane whatever the lane's depth: one wavefront per push / pop, where the local-memory
+ * stack costs one L1 wavefront per distinct depth in the warp and its lines are written back through L2 to DRAM);
+ * deeper entries overflow to the lane's local array.  0: the whole stack in local memory. */
+#ifndef RTC_SMEM_STACK
+#define RTC_SMEM_STACK 8
+#endif
 #define PRIM_NONE 0xFFFFFFFFu
 #define PRIM_MEDIUM_KIND 3u     /* best_prim = MAKE_REF(3, 0, medium index) for a medium hit */
 
@@ -278,9 +285,14 @@ RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float 
  * in the group's frame (rtc_bvh.cu), and only their own test moves the ray into their frame, op by op like
  * Translate_hit / RotateY_hit (hittable.c:325-367) -- the hit distance keeps the reference's bits, the walk never
  * changes frame. */
-struct Walker {
+extern __shared__ __align__(16) uint32_t rtc_dyn_smem[]; /* dynamic shared memory of the render kernels */
+
+template <int SK> struct WalkerT {
   uint32_t *stack;    /* TRACE_STACK entries owned by the caller (a separate local array, so that the scalar members
                          below stay in registers) */
+  uint32_t sbase;     /* SK > 0: shared-window address of this lane's column of the CTA's stack (rtc_dyn_smem:
+                         [entry][thread]); kept as a 32-bit address so that a push / pop is one LEA + STS / LDS */
+  uint32_t sstride;   /*         bytes between two entries = 4 * threads per CTA */
   int sp;
   float d_len2;       /* |d|^2 of the group-frame ray in the reference's operation order: the `a` of its sphere tests */
   SlabRay slab;
@@ -290,8 +302,20 @@ struct Walker {
 
   /* The ray itself and t_min are not kept here: the caller passes them to every leaf step (`outer` is a callable
    * returning the group-frame ray -- a register copy, or a reload from wherever the caller parked it). */
+  RTC_DEV void push(uint32_t v) {
+    if (SK > 0) {
+      if (sp < SK)
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(sbase + (uint32_t)sp * sstride), "r"(v) : "memory");
+      else
+        stack[sp - SK] = v;
+      sp++;
+    } else {
+      stack[sp++] = v;
+    }
+  }
   RTC_DEV void begin(uint32_t root, const Ray &ray, float tmax) {
-    stack[0] = REF_EMPTY, sp = 1; /* the bottom entry ends the walk: pop() needs no emptiness test */
+    sp = 0;
+    push(REF_EMPTY); /* the bottom entry ends the walk: pop() needs no emptiness test */
     d_len2 = sv_len2(ray.d), slab = slab_setup(ray);
     cur = root, best_node = 0;
     best.t = tmax, best.prim = PRIM_NONE, best.inst = RT_NONE;
@@ -300,7 +324,17 @@ struct Walker {
   RTC_DEV void resume(const Ray &ray) { d_len2 = sv_len2(ray.d), slab = slab_setup(ray); }
   RTC_DEV bool at_inner() const { return REF_KIND(cur) == REF_INNER; }
   RTC_DEV bool done() const { return cur == REF_EMPTY; }
-  RTC_DEV uint32_t pop() { return stack[--sp]; } /* never called once done(): the bottom entry is REF_EMPTY */
+  RTC_DEV uint32_t pop() { /* never called once done(): the bottom entry is REF_EMPTY */
+    --sp;
+    if (SK > 0) {
+      if (sp >= SK)
+        return stack[sp - SK];
+      uint32_t v;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sbase + (uint32_t)sp * sstride) : "memory");
+      return v;
+    }
+    return stack[sp];
+  }
 
   /* one inner node: both children's boxes, nearer child first, the other one pushed */
   template <bool NONNEG> RTC_DEV void visit(const DScene &sc, float t_min) {
@@ -318,7 +352,7 @@ struct Walker {
     if (h0 && h1) {
       const bool swap = e1 < e0;
       next = swap ? ch.y : ch.x;
-      stack[sp++] = swap ? ch.x : ch.y;
+      push(swap ? ch.x : ch.y);
     }
     if (!(h0 || h1))
       next = pop();
@@ -342,7 +376,7 @@ struct Walker {
     if (park)
       parked = next;
     if (both && !park)
-      stack[sp++] = far;
+      push(far);
     if (both && park)
       next = far;
     if (none || (park && !both))
@@ -366,6 +400,7 @@ struct Walker {
     cur = pop();
   }
 };
+typedef WalkerT<0> Walker; /* the whole stack in the caller's local array */
 
 /* One round of a WARP-SYNCHRONOUS walk (all 32 lanes call it together, a lane without a ray with w.done()):
  * descend while at least `thr8` eighths of the warp's busy lanes hold an inner node, then the lanes that hold a leaf
@@ -373,8 +408,8 @@ struct Walker {
  * a long descent keeps every lane that already has its leaf waiting -- ncu on Book 1: descents are geometric with
  * mean 3.5 visits, the longest of 32 is 10.7, so 10.6 of 32 lanes are active in the node loop.  Leaving the loop
  * early costs nothing: a lane that is still descending just carries on in the next round. */
-template <bool NONNEG, bool PARK, class Outer>
-RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer outer, int thr8) {
+template <bool NONNEG, bool PARK, class W, class Outer>
+RTC_DEV void walk_round_sync(const DScene &sc, W &w, float t_min, Outer outer, int thr8) {
   const unsigned busy = __ballot_sync(0xffffffffu, !w.done());
   const int thr = max(1, (__popc(busy) * thr8 + 7) >> 3);
   if (PARK) {
@@ -394,7 +429,7 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
       if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
         break;
       if (in)
-        w.visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
+        w.template visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
     }
     if (parked != REF_EMPTY)
       w.leaf_test(sc, parked, t_min, outer);
@@ -405,9 +440,9 @@ RTC_DEV void walk_round_sync(const DScene &sc, Walker &w, float t_min, Outer out
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
     if (in) { /* (RTC_VISITS_PER_VOTE = 2 halves the votes but measured slower: code size) */
-      w.visit<NONNEG>(sc, t_min);
+      w.template visit<NONNEG>(sc, t_min);
       if (RTC_VISITS_PER_VOTE > 1 && w.at_inner())
-        w.visit<NONNEG>(sc, t_min);
+        w.template visit<NONNEG>(sc, t_min);
     }
   }
   if (!w.at_inner() && !w.done())

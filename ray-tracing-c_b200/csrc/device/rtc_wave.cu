@@ -398,6 +398,7 @@ cudaError_t wave_render(const DScene &sc, const RenderJob &job, const WavePlan &
   const long long items_per_slot =
       ((long long)job.cam.img_width * job.cam.img_height * plan.mega.n_chunks + (long long)s - 1) / (long long)s + 1;
   const long long max_iters = 64 + items_per_slot * (long long)plan.mega.chunk * ((long long)job.cam.max_depth + 1);
+  bool finished = false;
   for (long long iter = 0; iter < max_iters;) {
     for (int k = 0; k < WAVE_BATCH; k++) {
       wave_extend_kernel<<<blocks, WAVE_BLOCK, 0, stream>>>(sc, job, pool, k & 1);
@@ -411,9 +412,13 @@ cudaError_t wave_render(const DScene &sc, const RenderJob &job, const WavePlan &
     if ((err = cudaMemcpyAsync(&done, &pool.ctl->done, 4, cudaMemcpyDeviceToHost, stream)) != cudaSuccess ||
         (err = cudaStreamSynchronize(stream)) != cudaSuccess)
       return err;
-    if (done >= plan.slots)
+    if (done >= plan.slots) {
+      finished = true;
       break;
+    }
   }
+  if (!finished) /* the iteration bound ran out with live paths: an incomplete frame is an error, not a result */
+    return cudaErrorLaunchTimeout;
   if (plan.mega.n_chunks > 1) {
     size_t n_values = (size_t)job.cam.img_width * job.cam.img_height * 3;
     wave_sum_chunks_kernel<<<(unsigned)((n_values + 255) / 256), 256, 0, stream>>>(partial, job.radiance, n_values,

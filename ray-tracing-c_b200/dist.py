@@ -62,16 +62,24 @@ class DistRenderer:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
 
-    def enqueue(self, kernel="mega", rng="sample", drop_nan=False):
-        """Launch this rank's shard + the reduce + (rank 0) tonemap and D2H on the current stream; asynchronous."""
-        spp = self.camera.samples_per_pixel
+    def enqueue(self, kernel="mega", rng="sample", drop_nan=False, spp=None):
+        """Launch this rank's shard + the reduce + (rank 0) tonemap and D2H on the current stream; asynchronous.
+        `spp` renders only the first spp samples of every pixel (warm-up steps of minute-long frames)."""
+        spp = int(spp or self.camera.samples_per_pixel)
         begin, count = shard_range(spp, self.rank, self.world)
         if self.world > 1 and rng != "sample":
             raise ValueError("a sample-range shard needs per-sample RNG streams (rng='sample')")
+        if count <= 0:
+            raise ValueError("fewer samples than ranks")
         opts = make_opts(kernel=kernel, rng=rng, sample_begin=begin, sample_count=count, drop_nan=drop_nan)
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
         self.scene.render_device(self.camera, opts, self.radiance.data_ptr(), stream)
+        if self.world > 1:  # the path's one exchange step, event-timed on its own
+            self._reduce_ev = (self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True))
+            self._reduce_ev[0].record()
         reduce_radiance(self.radiance, 0, self.group)
+        if self.world > 1:
+            self._reduce_ev[1].record()
         if self.rank == 0:
             rc = lib.b200().rt_tonemap_device(self.radiance.data_ptr(), self.radiance.numel(), spp,
                                               self.rgb8.data_ptr(), stream or None)
@@ -79,14 +87,34 @@ class DistRenderer:
             self.host_rgb8.copy_(self.rgb8, non_blocking=True)
 
     def stats(self) -> dict:
+        """Counters of the last enqueue (synchronises the stream).  `reduce_ms`: device time between the end of this
+        rank's render kernel and the end of the NCCL reduce on this rank -- the wait for the slowest rank included."""
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
-        return self.scene.device_stats(stream)
+        st = self.scene.device_stats(stream)
+        ev = getattr(self, "_reduce_ev", None)
+        st["reduce_ms"] = float(ev[0].elapsed_time(ev[1])) if ev is not None else 0.0
+        return st
 
-    def render(self, kernel="mega", rng="sample", drop_nan=False):
-        self.enqueue(kernel, rng, drop_nan)
+    def render(self, kernel="mega", rng="sample", drop_nan=False, spp=None):
+        self.enqueue(kernel, rng, drop_nan, spp)
         st = self.stats()  # synchronises the stream
         image = self.host_rgb8.numpy().copy() if self.rank == 0 else None
         return image, st
+
+    def render_whole(self, kernel="mega", rng="sample"):
+        """ALL samples of every pixel on THIS rank's GPU alone (no collective): (rgb8, float radiance sum) as numpy.
+        bench.py's image_check compares it with the image the N ranks reduced."""
+        torch = self.torch
+        spp = int(self.camera.samples_per_pixel)
+        whole = torch.empty_like(self.radiance)
+        rgb8 = torch.empty_like(self.rgb8)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        opts = make_opts(kernel=kernel, rng=rng, sample_begin=0, sample_count=spp)
+        self.scene.render_device(self.camera, opts, whole.data_ptr(), stream)
+        lib.check(lib.b200().rt_tonemap_device(whole.data_ptr(), whole.numel(), spp, rgb8.data_ptr(), stream or None),
+                  "rt_tonemap_device")
+        torch.cuda.synchronize(self.device)
+        return rgb8.cpu().numpy(), whole.cpu().numpy()
 
     def total_segments(self, local_segments: int) -> int:
         """Whole-job segment count (all ranks), on every rank."""

@@ -123,6 +123,8 @@ def host() -> C.CDLL:
     lib.rtc_scene_desc_free.argtypes = [C.POINTER(abi.rt_scene_desc)]
     lib.rtc_scene_desc_free.restype = None
     lib.rtc_flatten_error.restype = C.c_char_p
+    lib.rtc_synthetic_image.argtypes = [i32, i32, vp]
+    lib.rtc_synthetic_image.restype = None
     lib.rtc_scene_title.argtypes = [i32]
     lib.rtc_scene_title.restype = C.c_char_p
     _host = lib

@@ -9,6 +9,12 @@ Per scene the fixture holds what the reference itself produced:
   rays_*        a fixed ray batch (camera rays, box-interior rays, axis-parallel edge cases) with per-ray PCG32 state
   hit_*         world.objects.hit() of the reference on that batch: t, p, normal, u, v, hit, front_face, material,
                 advanced rng state
+`python tests/golden/make_golden.py frames` writes tests/golden/frames.npz: the reference's own Camera_render
+(src/raytracing.c:86-135, per-pixel seeds (17+j, 23+i)) at REAL geometry and sample counts -- Book 1 final 400x225 at
+256 spp, Cornell box 200x200 at 256 spp, Book 2 final 200x200 at 128 spp, depth 50 -- as 8-bit frames, plus for the
+noise floor the same frames from independent streams: the oracle in LIBM mode (pinned byte-identical to the reference
+by test_oracle_golden.py) with the per-(pixel, sample) seeds.  The megakernel is tested against these on the GPU box.
+
 The GPU box has no /root/reference; tests there pin the oracle (and the host layer) against these files.
 """
 from __future__ import annotations
@@ -90,5 +96,42 @@ def main():
               f"blob {len(blob)} B -> {out.name} ({out.stat().st_size} B)")
 
 
+FRAMES = [  # scene, width, spp: BASELINE.json configs 2, 3, 4 at a third / a fifth of their linear size
+    (1, 400, 256),
+    (6, 200, 256),
+    (7, 200, 128),
+]
+
+
+def frames():
+    import oracle_lib as O
+
+    if not REF_TOOL.exists():
+        subprocess.run(["make", "-C", str(ROOT / "oracle"), "ref"], check=True)
+    out = {}
+    for scene_id, width, spp in FRAMES:
+        with tempfile.TemporaryDirectory() as tmp:
+            run(["render", scene_id, width, spp, DEPTH, 0, "out.rgb8", "camera.bin"], tmp)
+            rgb8 = np.fromfile(os.path.join(tmp, "out.rgb8"), dtype=np.uint8)
+        height = len(rgb8) // (width * 3)
+        ref = rgb8.reshape(height, width, 3)
+        sess = rtc.Session(scene_id, width=width, spp=spp, depth=DEPTH)
+        assert (sess.height, sess.width) == (height, width)
+        other, _, _ = O.render(sess.flatten(), sess.camera, rtc.make_opts(kernel="exact", rng="sample"), O.MATH_LIBM)
+        d = ref.astype(np.float64) - other.astype(np.float64)
+        print(f"scene {scene_id}: {width}x{height}x{spp} spp; reference vs independent streams: RMSE "
+              f"{np.sqrt((d ** 2).mean(axis=(0, 1))) } /255 per channel, mean diff {d.mean(axis=(0, 1))}")
+        out[f"ref_{scene_id}"] = ref
+        out[f"other_{scene_id}"] = other
+        out[f"shape_{scene_id}"] = np.array([width, height, spp, DEPTH])
+    path = HERE / "frames.npz"
+    np.savez_compressed(path, **out)
+    print(f"-> {path.name} ({path.stat().st_size} B)")
+
+
 if __name__ == "__main__":
-    main()
+    what = sys.argv[1] if len(sys.argv) > 1 else "scenes"
+    if what in ("scenes", "all"):
+        main()
+    if what in ("frames", "all"):
+        frames()

@@ -15,6 +15,7 @@ oracle's counters on the same frame at 1-2 spp.
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import importlib
 import json
 import os
@@ -54,7 +55,7 @@ def cpu_reference(scene, width, aspect, spp):
         if scene in (3, 7):
             w, h = 1024, 512
             rgb = np.zeros((h, w, 3), np.uint8)
-            rtc.lib.host().rtc_synthetic_image(w, h, rgb.ctypes.data)
+            rtc.lib.host().rtc_synthetic_image(w, h, rgb.ctypes.data_as(C.c_void_p))
             with open(Path(tmp) / "earthmap.jpg", "wb") as f:
                 f.write(f"P6\n{w} {h}\n255\n".encode() + rgb.tobytes())
         t0 = time.perf_counter()
