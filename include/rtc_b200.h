@@ -230,6 +230,17 @@ int rt_device_count(void);
 int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene **out);
 void rt_scene_destroy(rt_scene *scene);
 
+/* The same through a small cache of uploaded scenes, keyed by a 128-bit hash of the CONTENT of `desc` (arrays, counts,
+ * roots) and the device: a second call with an equal description returns the resident copy instead of rebuilding the
+ * BVH and uploading again.  No pointer of the caller is retained.  Camera_render() uses this pair, so that a host
+ * program calling it repeatedly on one World (as the reference's main() would in a loop) pays the scene set-up once.
+ * rt_scene_release() hands the scene back (it stays resident, least recently used ones are evicted beyond four per
+ * device); rt_scene_destroy() on an acquired scene removes it for good.  rt_shutdown() frees every idle cached scene
+ * and the multi-GPU context (streams, NCCL communicator) that rt_render_multi() keeps between calls. */
+int rt_scene_acquire(const rt_scene_desc *desc, int device, rt_scene **out);
+void rt_scene_release(rt_scene *scene);
+void rt_shutdown(void);
+
 /* Host-only: validates `desc` and builds the rebuilt acceleration structure WITHOUT touching a device; reports its
  * shape.  (What rt_scene_create would upload.)  Works on machines without a GPU. */
 typedef struct rt_scene_info {
@@ -272,10 +283,13 @@ int rt_hit_batch(rt_scene *scene, uint32_t kernel, size_t n, const float *origin
                  float t_max, uint64_t *rng_io, float *out_t, uint32_t *out_node, float *out_p, float *out_normal,
                  float *out_uv, uint8_t *out_front, uint32_t *out_material);
 
-/* Single-process multi-GPU render through HOST buffers: replicates the scene on devices 0..n_gpus-1, gives
- * device g the sample range [g*spp/n, (g+1)*spp/n) (RT_RNG_SAMPLE streams), sums the per-device float buffers on
- * device 0 over NVLink peer copies and tonemaps there.  One-process-per-GPU drivers use rt_render_device + NCCL
- * instead (see ray-tracing-c_b200/dist.py). */
+/* Single-process multi-GPU render through HOST buffers (what Camera_render does under RT_GPUS=N): replicates the
+ * scene on devices 0..n_gpus-1 (through the scene cache), gives device g the sample range [g*spp/n, (g+1)*spp/n)
+ * (RT_RNG_SAMPLE streams), sums the per-device float frames onto device 0 with ONE ncclReduce(sum, float32, root 0)
+ * inside ncclGroupStart/End on a communicator created once with ncclCommInitAll and kept (NCCL is dlopen'ed:
+ * libnccl.so.2; without it, or with RT_MULTI_NCCL=0, the frames are gathered over peer copies and added on device 0),
+ * and tonemaps there.  One-process-per-GPU drivers use rt_render_device + their own NCCL reduce instead (see
+ * ray-tracing-c_b200/dist.py). */
 int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camera, const rt_opts *opts, int n_gpus,
                     float *radiance_sum, uint8_t *rgb8, rt_stats *stats);
 

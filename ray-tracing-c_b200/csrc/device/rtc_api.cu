@@ -10,6 +10,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <dlfcn.h>
+#include <mutex>
+#include <nccl.h> /* types and prototypes only: the library itself is dlopen'ed (rt_render_multi) */
 #include <new>
 #include <vector>
 
@@ -63,6 +66,10 @@ struct rt_scene {
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   rt_stats last = {};
   int last_launches = 0;
+  /* scene cache (rt_scene_acquire / rt_scene_release) */
+  bool cached = false, in_use = false;
+  uint64_t key[2] = {0, 0};
+  uint64_t last_use = 0;
 };
 
 namespace {
@@ -140,9 +147,7 @@ int ensure(void **ptr, size_t *have, size_t need) {
 
 } // namespace
 
-extern "C" void rt_scene_destroy(rt_scene *scene) {
-  if (!scene)
-    return;
+static void scene_free(rt_scene *scene) {
   DeviceGuard guard(scene->device);
   cudaDeviceSynchronize(); /* renders enqueued on caller streams (rt_render_device) may still be running */
   for (void *p : scene->allocations)
@@ -155,6 +160,139 @@ extern "C" void rt_scene_destroy(rt_scene *scene) {
     if (e)
       cudaEventDestroy(e);
   delete scene;
+}
+
+/* ------------------------------------------------------------------ scene cache -------------------------- */
+
+/* Camera_render builds, uploads and destroys one scene per call, like the reference (which holds nothing between
+ * calls).  For a frame that takes 30 ms on eight GPUs the flatten + SAH build + upload is 1 ms of it, so uploaded
+ * scenes are kept, keyed by a 128-bit hash of the CONTENT of the description (no pointer of the caller is retained):
+ * a caller that renders the same World again gets the resident copy. */
+namespace {
+std::mutex g_cache_mutex;
+std::vector<rt_scene *> g_cache;
+uint64_t g_cache_clock = 0;
+constexpr size_t kCachePerDevice = 4;
+
+inline uint64_t mix64(uint64_t h, uint64_t v, uint64_t mul) {
+  h ^= v;
+  h *= mul;
+  return h ^ (h >> 29);
+}
+void hash_bytes(const void *data, size_t bytes, uint64_t key[2]) {
+  /* four independent lanes over 32-byte blocks (a single multiply chain would be latency-bound: the image texture
+   * of the Book 2 scene alone is 1.5 MB), folded into two 64-bit words */
+  const uint8_t *p = static_cast<const uint8_t *>(data);
+  uint64_t a = key[0] ^ 0x9E3779B97F4A7C15ull, b = key[1] ^ 0xC2B2AE3D27D4EB4Full, c = bytes, d = ~bytes;
+  size_t n = bytes / 32;
+  for (size_t i = 0; i < n; i++, p += 32) {
+    uint64_t w[4];
+    memcpy(w, p, 32);
+    a = mix64(a, w[0], 0xFF51AFD7ED558CCDull), b = mix64(b, w[1], 0xC4CEB9FE1A85EC53ull);
+    c = mix64(c, w[2], 0x9FB21C651E98DF25ull), d = mix64(d, w[3], 0xD6E8FEB86659FD93ull);
+  }
+  uint64_t tail[4] = {0, 0, 0, 0};
+  memcpy(tail, p, bytes % 32);
+  a = mix64(a, tail[0], 0xFF51AFD7ED558CCDull), b = mix64(b, tail[1], 0xC4CEB9FE1A85EC53ull);
+  c = mix64(c, tail[2], 0x9FB21C651E98DF25ull), d = mix64(d, tail[3], 0xD6E8FEB86659FD93ull);
+  key[0] = mix64(mix64(a, c, 0x94D049BB133111EBull), b, 0xBF58476D1CE4E5B9ull);
+  key[1] = mix64(mix64(b, d, 0xBF58476D1CE4E5B9ull), a, 0x94D049BB133111EBull);
+}
+void hash_desc(const rt_scene_desc &d, uint64_t key[2]) {
+  key[0] = key[1] = 0;
+  const uint32_t head[12] = {d.abi_version, d.n_nodes,  d.n_children, d.n_spheres,    d.n_quads,    d.n_materials,
+                             d.n_textures,  d.n_perlins, d.n_images,   d.objects_root, d.lights_root, 0};
+  hash_bytes(head, sizeof(head), key);
+  hash_bytes(&d.n_texel_bytes, sizeof(d.n_texel_bytes), key);
+  hash_bytes(d.nodes, sizeof(rt_node) * d.n_nodes, key);
+  hash_bytes(d.children, 4ull * d.n_children, key);
+  hash_bytes(d.spheres, sizeof(rt_sphere) * d.n_spheres, key);
+  hash_bytes(d.quads, sizeof(rt_quad) * d.n_quads, key);
+  hash_bytes(d.materials, sizeof(rt_material) * d.n_materials, key);
+  hash_bytes(d.textures, sizeof(rt_texture) * d.n_textures, key);
+  hash_bytes(d.perlins, sizeof(rt_perlin) * d.n_perlins, key);
+  hash_bytes(d.images, sizeof(rt_image) * d.n_images, key);
+  hash_bytes(d.texels, d.n_texel_bytes, key);
+}
+} // namespace
+
+extern "C" void rt_scene_destroy(rt_scene *scene) {
+  if (!scene)
+    return;
+  if (scene->cached) { /* destroying a cached scene takes it out of the cache */
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    for (size_t i = 0; i < g_cache.size(); i++)
+      if (g_cache[i] == scene) {
+        g_cache.erase(g_cache.begin() + (long)i);
+        break;
+      }
+  }
+  scene_free(scene);
+}
+
+extern "C" int rt_scene_acquire(const rt_scene_desc *desc, int device, rt_scene **out) {
+  if (!desc || !out)
+    return fail(RT_ERR_INVALID, "rt_scene_acquire: NULL argument");
+  *out = nullptr;
+  std::string why = rtc_validate_desc(*desc);
+  if (!why.empty())
+    return fail(RT_ERR_INVALID, "rt_scene_acquire: %s", why.c_str());
+  if (rt_device_count() <= 0)
+    return fail(RT_ERR_NO_DEVICE, "rt_scene_acquire: no CUDA device (this library does not compute on the host)");
+  if (device < 0)
+    CUDA_TRY(cudaGetDevice(&device));
+  uint64_t key[2];
+  hash_desc(*desc, key);
+  {
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    for (rt_scene *s : g_cache)
+      if (!s->in_use && s->device == device && s->key[0] == key[0] && s->key[1] == key[1]) {
+        s->in_use = true;
+        s->last_use = ++g_cache_clock;
+        *out = s;
+        return RT_OK;
+      }
+  }
+  rt_scene *s = nullptr;
+  int rc = rt_scene_create(desc, device, &s);
+  if (rc != RT_OK)
+    return rc;
+  s->key[0] = key[0], s->key[1] = key[1];
+  s->cached = true, s->in_use = true;
+  std::vector<rt_scene *> evict;
+  {
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    s->last_use = ++g_cache_clock;
+    g_cache.push_back(s);
+    for (;;) { /* least recently used idle scenes of this device beyond the capacity */
+      size_t count = 0, oldest = g_cache.size();
+      for (size_t i = 0; i < g_cache.size(); i++)
+        if (g_cache[i]->device == device) {
+          count++;
+          if (!g_cache[i]->in_use && (oldest == g_cache.size() || g_cache[i]->last_use < g_cache[oldest]->last_use))
+            oldest = i;
+        }
+      if (count <= kCachePerDevice || oldest == g_cache.size())
+        break;
+      evict.push_back(g_cache[oldest]);
+      g_cache.erase(g_cache.begin() + (long)oldest);
+    }
+  }
+  for (rt_scene *e : evict)
+    scene_free(e);
+  *out = s;
+  return RT_OK;
+}
+
+extern "C" void rt_scene_release(rt_scene *scene) {
+  if (!scene)
+    return;
+  if (!scene->cached) {
+    scene_free(scene);
+    return;
+  }
+  std::lock_guard<std::mutex> lock(g_cache_mutex);
+  scene->in_use = false;
 }
 
 extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene **out) {
@@ -222,6 +360,21 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   v.world_root = built.world_root;
   v.n_media = (uint32_t)built.media.size();
   v.n_perlins = desc->n_perlins;
+  v.feats = (built.n_mquads ? FEAT_QUADS : 0) | (built.n_insts ? FEAT_INSTANCES : 0) |
+            (desc->lights_root != RT_NONE ? FEAT_LIGHTS : 0) | (built.media.empty() ? 0 : FEAT_MEDIA);
+  for (uint32_t k = 0; k < desc->n_textures; k++)
+    if (desc->textures[k].kind != RT_TEX_SOLID)
+      v.feats |= FEAT_TEXTURES;
+  for (uint32_t k = 0; k < desc->n_materials; k++)
+    if (desc->materials[k].tag == RT_MAT_ISOTROPIC)
+      v.feats |= FEAT_MEDIA;
+  if (desc->lights_root != RT_NONE && getenv("RT_ONE_LIGHT_OFF") == nullptr) {
+    const rt_node &l = desc->nodes[desc->lights_root];
+    if (l.kind == RT_NODE_LIST && l.b == 1 && desc->nodes[desc->children[l.a]].kind == RT_NODE_QUAD) {
+      v.one_quad_light = 1;
+      v.light = desc->quads[desc->nodes[desc->children[l.a]].a];
+    }
+  }
   if (rc == RT_OK) {
     cudaError_t err = dev_alloc((void **)&s->counters, sizeof(RenderCounters));
     for (int k = 0; k < 4 && err == cudaSuccess; k++)
@@ -346,7 +499,7 @@ static int enqueue_render(rt_scene *s, const rt_camera *cam, const rt_opts *opts
     const int scene_class = s->view.n_media           ? MEGA_SCENE_MEDIA
                             : s->built_info.n_mquads ? MEGA_SCENE_QUADS
                                                      : MEGA_SCENE_SPHERES;
-    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, scene_class, &plan));
+    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, scene_class, (int)s->view.feats, &plan));
     rc = ensure(&s->scratch, &s->scratch_bytes, plan.partial_bytes);
     if (rc != RT_OK)
       return rc;
@@ -513,6 +666,138 @@ __global__ void add_into_kernel(float *__restrict__ acc, const float *__restrict
     acc[i] += other[i];
 }
 
+namespace {
+
+/* NCCL is loaded at run time (libnccl.so.2: the system library, or the one a host program such as PyTorch has
+ * already mapped), so that librtc_b200.so has no link-time dependency on it; without it rt_render_multi gathers
+ * over peer copies instead. */
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Reduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+};
+NcclApi &nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried)
+    return api;
+  tried = true;
+  const char *off = getenv("RT_MULTI_NCCL");
+  if (off && off[0] == '0')
+    return api;
+  api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!api.handle)
+    api.handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!api.handle)
+    return api;
+#define NCCL_SYM(field, name) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, name))
+  NCCL_SYM(CommInitAll, "ncclCommInitAll");
+  NCCL_SYM(CommDestroy, "ncclCommDestroy");
+  NCCL_SYM(Reduce, "ncclReduce");
+  NCCL_SYM(GroupStart, "ncclGroupStart");
+  NCCL_SYM(GroupEnd, "ncclGroupEnd");
+  NCCL_SYM(GetErrorString, "ncclGetErrorString");
+#undef NCCL_SYM
+  api.ok = api.CommInitAll && api.CommDestroy && api.Reduce && api.GroupStart && api.GroupEnd && api.GetErrorString;
+  return api;
+}
+
+/* what rt_render_multi keeps between calls: one stream and one event per device, the communicator (creating one
+ * costs hundreds of milliseconds -- SURVEY.md 8(d) asks for it to be cached), staging for the peer-copy path */
+struct MultiContext {
+  int n = 0;
+  bool nccl = false;
+  std::vector<ncclComm_t> comms;
+  std::vector<cudaStream_t> streams;
+  std::vector<cudaEvent_t> done;
+  float *staging = nullptr; /* device 0, peer-copy path only */
+  size_t staging_bytes = 0;
+};
+MultiContext g_multi;
+std::mutex g_multi_mutex;
+
+void multi_teardown() {
+  MultiContext &m = g_multi;
+  for (int g = 0; g < m.n; g++) {
+    cudaSetDevice(g);
+    if (g < (int)m.comms.size() && m.comms[g])
+      nccl_api().CommDestroy(m.comms[g]);
+    if (g < (int)m.streams.size() && m.streams[g])
+      cudaStreamDestroy(m.streams[g]);
+    if (g < (int)m.done.size() && m.done[g])
+      cudaEventDestroy(m.done[g]);
+  }
+  if (m.staging) {
+    cudaSetDevice(0);
+    dev_free(m.staging);
+  }
+  m = MultiContext();
+}
+
+int multi_setup(int n_gpus) {
+  MultiContext &m = g_multi;
+  if (m.n == n_gpus)
+    return RT_OK;
+  multi_teardown();
+  m.streams.assign(n_gpus, nullptr), m.done.assign(n_gpus, nullptr), m.comms.assign(n_gpus, nullptr);
+  m.n = n_gpus;
+  for (int g = 0; g < n_gpus; g++) {
+    CUDA_TRY(cudaSetDevice(g));
+    CUDA_TRY(cudaStreamCreateWithFlags(&m.streams[g], cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&m.done[g], cudaEventDisableTiming));
+  }
+  NcclApi &api = nccl_api();
+  if (api.ok) {
+    std::vector<int> devs(n_gpus);
+    for (int g = 0; g < n_gpus; g++)
+      devs[g] = g;
+    ncclResult_t r = api.CommInitAll(m.comms.data(), n_gpus, devs.data());
+    if (r == ncclSuccess) {
+      m.nccl = true;
+    } else {
+      fprintf(stderr, "rtc_b200: ncclCommInitAll failed (%s); gathering over peer copies\n", api.GetErrorString(r));
+      m.comms.assign(n_gpus, nullptr);
+    }
+  }
+  if (!m.nccl)
+    for (int g = 1; g < n_gpus; g++) { /* peer copies go over NVLink when access is enabled */
+      int can = 0;
+      cudaSetDevice(0);
+      if (cudaDeviceCanAccessPeer(&can, 0, g) == cudaSuccess && can && cudaDeviceEnablePeerAccess(g, 0) != cudaSuccess)
+        cudaGetLastError(); /* already enabled */
+    }
+  return RT_OK;
+}
+
+} // namespace
+
+/* Frees what the library keeps between calls: cached scenes that are not in use, the multi-GPU context. */
+extern "C" void rt_shutdown(void) {
+  std::vector<rt_scene *> idle;
+  {
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    for (size_t i = 0; i < g_cache.size();)
+      if (!g_cache[i]->in_use) {
+        idle.push_back(g_cache[i]);
+        g_cache.erase(g_cache.begin() + (long)i);
+      } else {
+        i++;
+      }
+  }
+  for (rt_scene *s : idle)
+    scene_free(s);
+  std::lock_guard<std::mutex> lock(g_multi_mutex);
+  int previous = 0;
+  cudaGetDevice(&previous);
+  multi_teardown();
+  cudaSetDevice(previous);
+}
+
 extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camera, const rt_opts *opts, int n_gpus,
                                float *radiance_sum, uint8_t *rgb8, rt_stats *stats) {
   if (!desc || !camera || !opts || n_gpus < 1)
@@ -531,57 +816,51 @@ extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camer
   if (count < n_gpus)
     return fail(RT_ERR_INVALID, "rt_render_multi: fewer samples than GPUs");
 
+  std::lock_guard<std::mutex> lock(g_multi_mutex);
+  int previous = 0;
+  cudaGetDevice(&previous);
   const size_t n_values = (size_t)camera->img_width * camera->img_height * 3;
   std::vector<rt_scene *> scenes(n_gpus, nullptr);
-  std::vector<cudaStream_t> streams(n_gpus, nullptr);
-  std::vector<float *> staging(n_gpus, nullptr); /* on device 0, one per peer */
-  std::vector<cudaEvent_t> done(n_gpus, nullptr);
-  auto cleanup = [&]() {
-    for (int g = 0; g < n_gpus; g++) {
+  /* every exit path: wait for the devices, give the scenes back to the cache, restore the caller's device */
+  auto finish = [&](int status) {
+    for (int g = 0; g < n_gpus; g++)
       if (scenes[g]) {
-        cudaSetDevice(scenes[g]->device);
-        if (streams[g])
-          cudaStreamDestroy(streams[g]);
-        if (done[g])
-          cudaEventDestroy(done[g]);
+        cudaSetDevice(g);
+        cudaStreamSynchronize(g_multi.streams[g]);
+        rt_scene_release(scenes[g]);
       }
-      rt_scene_destroy(scenes[g]);
-    }
-    cudaSetDevice(0);
-    for (float *p : staging)
-      if (p)
-        cudaFree(p);
+    cudaSetDevice(previous);
+    return status;
   };
 #define MULTI_TRY(expr)                                                                                              \
   do {                                                                                                               \
     cudaError_t err__ = (expr);                                                                                      \
-    if (err__ != cudaSuccess) {                                                                                      \
-      cleanup();                                                                                                     \
-      return fail(RT_ERR_CUDA, "rt_render_multi: %s: %s", #expr, cudaGetErrorString(err__));                         \
-    }                                                                                                                \
+    if (err__ != cudaSuccess)                                                                                        \
+      return finish(fail(RT_ERR_CUDA, "rt_render_multi: %s: %s", #expr, cudaGetErrorString(err__)));                 \
   } while (0)
 
-  int previous = 0;
-  cudaGetDevice(&previous);
-  for (int g = 0; g < n_gpus && rc == RT_OK; g++) {
-    rc = rt_scene_create(desc, g, &scenes[g]);
-    if (rc != RT_OK)
-      break;
-    MULTI_TRY(cudaSetDevice(g));
-    MULTI_TRY(cudaStreamCreateWithFlags(&streams[g], cudaStreamNonBlocking));
-    MULTI_TRY(cudaEventCreateWithFlags(&done[g], cudaEventDisableTiming));
-    rc = ensure((void **)&scenes[g]->radiance, &scenes[g]->radiance_bytes, n_values * sizeof(float));
-  }
+  rc = multi_setup(n_gpus);
   if (rc != RT_OK) {
-    cleanup();
     cudaSetDevice(previous);
     return rc;
   }
+  MultiContext &m = g_multi;
+  for (int g = 0; g < n_gpus; g++) {
+    rc = rt_scene_acquire(desc, g, &scenes[g]);
+    if (rc == RT_OK) {
+      MULTI_TRY(cudaSetDevice(g));
+      rc = ensure((void **)&scenes[g]->radiance, &scenes[g]->radiance_bytes, n_values * sizeof(float));
+    }
+    if (rc != RT_OK)
+      return finish(rc);
+  }
   MULTI_TRY(cudaSetDevice(0));
   rc = ensure((void **)&scenes[0]->rgb8, &scenes[0]->rgb8_bytes, n_values);
-  for (int g = 1; g < n_gpus; g++)
-    MULTI_TRY(cudaMalloc(&staging[g], n_values * sizeof(float)));
-  MULTI_TRY(cudaEventRecord(scenes[0]->ev[0], streams[0]));
+  if (rc == RT_OK && !m.nccl && n_gpus > 1)
+    rc = ensure((void **)&m.staging, &m.staging_bytes, n_values * sizeof(float));
+  if (rc != RT_OK)
+    return finish(rc);
+  MULTI_TRY(cudaEventRecord(scenes[0]->ev[0], m.streams[0]));
 
   /* sample range of GPU g: [begin + g*count/n, begin + (g+1)*count/n) */
   for (int g = 0; g < n_gpus; g++) {
@@ -589,39 +868,48 @@ extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camer
     rt_opts mine = base;
     mine.sample_begin = begin + (int)((long long)count * g / n_gpus);
     mine.sample_count = begin + (int)((long long)count * (g + 1) / n_gpus) - mine.sample_begin;
-    rc = enqueue_render(scenes[g], camera, &mine, scenes[g]->radiance, streams[g]);
-    if (rc != RT_OK) {
-      cleanup();
-      cudaSetDevice(previous);
-      return rc;
-    }
-    MULTI_TRY(cudaEventRecord(done[g], streams[g]));
+    rc = enqueue_render(scenes[g], camera, &mine, scenes[g]->radiance, m.streams[g]);
+    if (rc != RT_OK)
+      return finish(rc);
+    MULTI_TRY(cudaEventRecord(m.done[g], m.streams[g]));
   }
-  /* gather over peer copies (NVLink when peer access exists) and sum on device 0 in GPU order */
-  MULTI_TRY(cudaSetDevice(0));
-  const unsigned blocks = (unsigned)((n_values + 255) / 256);
-  for (int g = 1; g < n_gpus; g++) {
-    MULTI_TRY(cudaStreamWaitEvent(streams[0], done[g], 0));
-    MULTI_TRY(cudaMemcpyPeerAsync(staging[g], 0, scenes[g]->radiance, g, n_values * sizeof(float), streams[0]));
-    add_into_kernel<<<blocks, 256, 0, streams[0]>>>(scenes[0]->radiance, staging[g], n_values);
-    MULTI_TRY(cudaGetLastError());
+  if (m.nccl && n_gpus > 1) {
+    /* the path's one exchange step: sum of the per-device float frames onto device 0 (in place), NCCL over NVLink */
+    NcclApi &api = nccl_api();
+    ncclResult_t r = api.GroupStart();
+    for (int g = 0; g < n_gpus && r == ncclSuccess; g++)
+      r = api.Reduce(scenes[g]->radiance, scenes[g]->radiance, n_values, ncclFloat, ncclSum, 0, m.comms[g],
+                     m.streams[g]);
+    ncclResult_t r_end = api.GroupEnd();
+    if (r == ncclSuccess)
+      r = r_end;
+    if (r != ncclSuccess)
+      return finish(fail(RT_ERR_CUDA, "rt_render_multi: ncclReduce: %s", api.GetErrorString(r)));
+    MULTI_TRY(cudaSetDevice(0));
+  } else {
+    /* gather over peer copies and sum on device 0 in GPU order */
+    MULTI_TRY(cudaSetDevice(0));
+    const unsigned blocks = (unsigned)((n_values + 255) / 256);
+    for (int g = 1; g < n_gpus; g++) {
+      MULTI_TRY(cudaStreamWaitEvent(m.streams[0], m.done[g], 0));
+      MULTI_TRY(cudaMemcpyPeerAsync(m.staging, 0, scenes[g]->radiance, g, n_values * sizeof(float), m.streams[0]));
+      add_into_kernel<<<blocks, 256, 0, m.streams[0]>>>(scenes[0]->radiance, m.staging, n_values);
+      MULTI_TRY(cudaGetLastError());
+    }
   }
   if (rgb8) {
-    rc = rt_tonemap_device(scenes[0]->radiance, n_values, count, scenes[0]->rgb8, streams[0]);
-    if (rc != RT_OK) {
-      cleanup();
-      cudaSetDevice(previous);
-      return rc;
-    }
-    MULTI_TRY(cudaMemcpyAsync(rgb8, scenes[0]->rgb8, n_values, cudaMemcpyDeviceToHost, streams[0]));
+    rc = rt_tonemap_device(scenes[0]->radiance, n_values, count, scenes[0]->rgb8, m.streams[0]);
+    if (rc != RT_OK)
+      return finish(rc);
+    MULTI_TRY(cudaMemcpyAsync(rgb8, scenes[0]->rgb8, n_values, cudaMemcpyDeviceToHost, m.streams[0]));
   }
   if (radiance_sum)
     MULTI_TRY(cudaMemcpyAsync(radiance_sum, scenes[0]->radiance, n_values * sizeof(float), cudaMemcpyDeviceToHost,
-                              streams[0]));
-  MULTI_TRY(cudaEventRecord(scenes[0]->ev[3], streams[0]));
+                              m.streams[0]));
+  MULTI_TRY(cudaEventRecord(scenes[0]->ev[3], m.streams[0]));
   for (int g = 0; g < n_gpus; g++) {
     MULTI_TRY(cudaSetDevice(g));
-    MULTI_TRY(cudaStreamSynchronize(streams[g]));
+    MULTI_TRY(cudaStreamSynchronize(m.streams[g]));
   }
   rt_stats total;
   memset(&total, 0, sizeof(total));
@@ -636,12 +924,10 @@ extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camer
     if (g == 0)
       total.total_ms = st.total_ms;
   }
-  total.launches += (uint32_t)(n_gpus - 1) + (rgb8 ? 1u : 0u);
+  total.launches += (m.nccl ? 0u : (uint32_t)(n_gpus - 1)) + (rgb8 ? 1u : 0u);
   if (stats && rc == RT_OK)
     *stats = total;
-  cleanup();
-  cudaSetDevice(previous);
-  return rc;
+  return finish(rc);
 #undef MULTI_TRY
 }
 

@@ -224,8 +224,8 @@ struct Box {
 };
 
 struct Item {
-  uint32_t kind;  /* REF_SPHERES / REF_QUADS */
-  uint32_t index; /* desc sphere / desc quad */
+  uint32_t kind;  /* REF_SPHERES / REF_QUADS / REF_BOXES */
+  uint32_t index; /* desc sphere / desc quad / first slot in desc.children of the Box's six quads */
   uint32_t tag;   /* 0: in the group's own frame; k: under out.insts[k-1]'s transform chain */
   Box box;        /* in the group's frame */
 };
@@ -236,11 +236,14 @@ static float env_float(const char *name, float fallback) {
   return v && *v ? (float)atof(v) : fallback;
 }
 static const float kCostNode = 1.0f, kCostSphere = env_float("RT_BVH_COST_SPHERE", 0.8f),
-                   kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f);
+                   kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f), kCostBox = env_float("RT_BVH_COST_BOX", 4.0f);
+/* RT_BVH_BOXES=0: every quad its own leaf (the round-1 structure), for A/B measurements; read at every build */
+static bool box_leaves_enabled() { return env_float("RT_BVH_BOXES", 1.0f) != 0.0f; }
 
 struct Builder {
   const rt_scene_desc &d;
   BuiltScene &out;
+  const bool kBoxLeaves = box_leaves_enabled();
   Builder(const rt_scene_desc &desc, BuiltScene &o) : d(desc), out(o) {}
 
   static Box node_box(const rt_node &n) {
@@ -249,7 +252,9 @@ struct Builder {
       b.lo[a] = n.bbox[2 * a], b.hi[a] = n.bbox[2 * a + 1];
     return b;
   }
-  static float item_cost(uint32_t kind) { return kind == REF_SPHERES ? kCostSphere : kCostQuad; }
+  static float item_cost(uint32_t kind) {
+    return kind == REF_SPHERES ? kCostSphere : kind == REF_BOXES ? kCostBox : kCostQuad;
+  }
 
   void unsupported(const std::string &why) {
     if (out.mega_supported) {
@@ -332,35 +337,65 @@ struct Builder {
    * each remembering the chain its own test has to apply to the ray.  (The reference never bounds its instances:
    * Translate_hit / RotateY_hit always enter the child, hittable.c:325-367.) */
   static constexpr uint32_t kTagPending = 0xFFFFFFFFu; /* a chain whose Instance is made by its first primitive */
+  int bvh_above = 0;               /* BVHNodes between the group's root and the node collect() is looking at */
+  std::set<uint32_t> media_in_bvh; /* media met below a BVHNode (see MMedium::in_list) */
+  uint32_t new_instance(const std::vector<ChainOp> &chain) {
+    if (out.insts.size() >= REF_MAX_TAG)
+      unsupported("more than 255 distinct Translate/RotateY chains in the scene");
+    Instance inst;
+    inst.op_begin = (uint32_t)out.ops.size();
+    inst.op_count = (uint32_t)chain.size();
+    inst.pad0 = inst.pad1 = 0;
+    out.ops.insert(out.ops.end(), chain.begin(), chain.end());
+    out.insts.push_back(inst);
+    return std::min<uint32_t>((uint32_t)out.insts.size(), REF_MAX_TAG);
+  }
   void collect(uint32_t id, std::vector<Item> &items, std::vector<ChainOp> &chain, uint32_t &tag,
                std::set<uint32_t> &seen, bool in_boundary,
                std::vector<std::pair<uint32_t, std::vector<ChainOp>>> &media) {
     const rt_node &n = d.nodes[id];
     switch (n.kind) {
-    case RT_NODE_LIST:
-      for (uint32_t k = 0; k < n.b; k++)
-        collect(d.children[n.a + k], items, chain, tag, seen, in_boundary, media);
+    case RT_NODE_LIST: {
+      /* a list of exactly six quads none of which was met before: what Box_new builds (hittable.c:246-264).  ONE leaf
+       * (any such list may be treated so: the leaf tests its quads in list order like HittableList_hit). */
+      bool six_quads = kBoxLeaves && n.b == 6 && out.mquads.size() + 6 < REF_MAX_INDEX;
+      for (uint32_t k = 0; six_quads && k < 6; k++) {
+        const uint32_t c = d.children[n.a + k];
+        six_quads = d.nodes[c].kind == RT_NODE_QUAD && !seen.count(c);
+        for (uint32_t j = 0; six_quads && j < k; j++)
+          six_quads = d.children[n.a + j] != c;
+      }
+      if (!six_quads) {
+        for (uint32_t k = 0; k < n.b; k++)
+          collect(d.children[n.a + k], items, chain, tag, seen, in_boundary, media);
+        break;
+      }
+      if (tag == kTagPending)
+        tag = new_instance(chain);
+      Item it;
+      it.kind = REF_BOXES, it.index = n.a, it.tag = tag;
+      it.box.reset();
+      for (uint32_t k = 0; k < 6; k++) {
+        const uint32_t c = d.children[n.a + k];
+        seen.insert(c);
+        it.box.grow(tag == 0 ? node_box(d.nodes[c]) : quad_box(d.quads[d.nodes[c].a], chain));
+      }
+      items.push_back(it);
       break;
+    }
     case RT_NODE_BVH:
+      bvh_above++;
       collect(n.a, items, chain, tag, seen, in_boundary, media);
       if (n.b != n.a)
         collect(n.b, items, chain, tag, seen, in_boundary, media);
+      bvh_above--;
       break;
     case RT_NODE_SPHERE:
     case RT_NODE_QUAD: {
       if (!seen.insert(id).second)
         break; /* the same object twice in one frame (BVH n==1 stores it as both children) */
-      if (tag == kTagPending) {
-        if (out.insts.size() >= REF_MAX_TAG)
-          unsupported("more than 255 distinct Translate/RotateY chains in the scene");
-        Instance inst;
-        inst.op_begin = (uint32_t)out.ops.size();
-        inst.op_count = (uint32_t)chain.size();
-        inst.pad0 = inst.pad1 = 0;
-        out.ops.insert(out.ops.end(), chain.begin(), chain.end());
-        out.insts.push_back(inst);
-        tag = std::min<uint32_t>((uint32_t)out.insts.size(), REF_MAX_TAG);
-      }
+      if (tag == kTagPending)
+        tag = new_instance(chain);
       Item it;
       it.kind = n.kind == RT_NODE_SPHERE ? REF_SPHERES : REF_QUADS;
       it.index = n.a;
@@ -387,8 +422,11 @@ struct Builder {
     case RT_NODE_MEDIUM:
       if (in_boundary)
         unsupported("a ConstantMedium inside the boundary of another ConstantMedium");
-      else
+      else {
         media.push_back(std::make_pair(id, chain));
+        if (bvh_above > 0)
+          media_in_bvh.insert(id);
+      }
       break;
     default: break;
     }
@@ -405,18 +443,21 @@ struct Builder {
       return MAKE_REF(REF_SPHERES, it.tag, at);
     }
     const uint32_t at = (uint32_t)out.mquads.size();
-    const rt_quad &q = d.quads[it.index];
-    MQuad mq;
-    float mat_bits, node_bits;
-    memcpy(&mat_bits, &q.material, 4);
-    memcpy(&node_bits, &q.node, 4);
-    mq.n_D = make_float4(q.normal[0], q.normal[1], q.normal[2], q.D);
-    mq.q_mat = make_float4(q.Q[0], q.Q[1], q.Q[2], mat_bits);
-    mq.w_nod = make_float4(q.w[0], q.w[1], q.w[2], node_bits);
-    mq.u_ar = make_float4(q.u[0], q.u[1], q.u[2], q.area);
-    mq.v_ = make_float4(q.v[0], q.v[1], q.v[2], 0.0f);
-    out.mquads.push_back(mq);
-    return MAKE_REF(REF_QUADS, it.tag, at);
+    const uint32_t count = it.kind == REF_BOXES ? 6u : 1u;
+    for (uint32_t k = 0; k < count; k++) {
+      const rt_quad &q = d.quads[it.kind == REF_BOXES ? d.nodes[d.children[it.index + k]].a : it.index];
+      MQuad mq;
+      float mat_bits, node_bits;
+      memcpy(&mat_bits, &q.material, 4);
+      memcpy(&node_bits, &q.node, 4);
+      mq.n_D = make_float4(q.normal[0], q.normal[1], q.normal[2], q.D);
+      mq.q_mat = make_float4(q.Q[0], q.Q[1], q.Q[2], mat_bits);
+      mq.w_nod = make_float4(q.w[0], q.w[1], q.w[2], node_bits);
+      mq.u_ar = make_float4(q.u[0], q.u[1], q.u[2], q.area);
+      mq.v_ = make_float4(q.v[0], q.v[1], q.v[2], 0.0f);
+      out.mquads.push_back(mq);
+    }
+    return MAKE_REF(it.kind, it.tag, at);
   }
 
   /* [lo, hi] as (centre, half extent) with [c - h, c + h] containing it.  The traversal computes the slab distances as
@@ -586,6 +627,7 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
     mm.material = n.b;
     mm.node = m.first;
     mm.neg_inv_density = n.f[0];
+    mm.in_list = b.media_in_bvh.count(m.first) ? 0u : 1u;
     out.media.push_back(mm);
   }
   out.n_bnodes = (uint32_t)out.bnodes.size(), out.n_msph = (uint32_t)out.msph.size();

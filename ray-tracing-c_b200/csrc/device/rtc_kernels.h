@@ -48,14 +48,25 @@ struct MegaPlan {
   int thr8;              /* node loop runs while >= thr8/8 of the busy lanes want it (walk_round_sync) */
   int resume8;           /* RESUME kernels: a trip's traversal ends once fewer than resume8/8 of its walkers remain */
   int cta8;              /* lockstep RESUME kernels: ... or once cta8/8 of the CTA's warps have finished theirs (0: off) */
-  int chunk;             /* samples per work item */
+  int chunk;             /* samples per work item: the first n_big items of a pixel */
+  int n_big, small;      /* ... the remaining items take `small` samples each (guided self-scheduling: the items handed
+                            out last are short, so the lanes finish close together; see mega_plan) */
   int n_chunks;          /* work items per pixel */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */
 };
+/* first sample (relative to the job's sample_begin) of a pixel's work item c; item c ends where item c + 1 begins */
+__host__ __device__ inline int plan_chunk_begin(const MegaPlan &p, int c) {
+#ifdef RTC_EXP_OLD_CHUNK
+  return c * p.chunk;
+#else
+  return c <= p.n_big ? c * p.chunk : p.n_big * p.chunk + (c - p.n_big) * p.small;
+#endif
+}
 /* what the scene contains, as far as the choice of kernel variant goes (rtc_mega.cu: mega_variant) */
 enum { MEGA_SCENE_SPHERES = 0, MEGA_SCENE_QUADS = 1, MEGA_SCENE_MEDIA = 2 };
+/* scene_feats: FEAT_* mask of the scene (rtc_scene.cuh): a kernel without the code of absent features is preferred */
 cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, int scene_class,
-                      MegaPlan *plan);
+                      int scene_feats, MegaPlan *plan);
 cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &plan, float *partial,
                         cudaStream_t stream, int *launches);
 cudaError_t mega_hit_batch(const DScene &sc, const HitBatch &b, cudaStream_t stream);

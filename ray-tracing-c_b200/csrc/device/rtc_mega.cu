@@ -101,7 +101,7 @@ RTC_DEV Ray camera_ray(const Frame &f, int pi, int pj, Rng &rng) {
 
 /* One step of Camera_ray_color (raytracing.c:39-72) for a path whose closest hit is `th`: adds what the hit emits,
  * scatters, updates the throughput.  Returns true when the path ended (its radiance L is final). */
-template <bool DEFER>
+template <bool DEFER, int FEATS = FEAT_ALL>
 RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th, Ray &ray, V3 &beta, V3 &L, int &depth,
                            Rng &rng, unsigned &n_pdf, PendingTex &pend) {
   if (th.prim == PRIM_NONE) {
@@ -109,7 +109,7 @@ RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th,
     return true;
   }
   Hit rec;
-  trace_finalize<false>(sc, ray, th, rec);
+  trace_finalize<false, FEATS>(sc, ray, th, rec);
   V3 r_out, albedo;
   bool skip_pdf;
   const uint32_t tag = __ldg(&sc.materials[rec.material].tag);
@@ -117,14 +117,31 @@ RTC_DEV bool shade_segment(const DScene &sc, const Frame &f, const TraceHit &th,
     L = v_add(L, v_mul(beta, material_emit<false>(sc, rec)));
     return true;
   }
-  if (!material_scatter<false, DEFER>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng, pend))
+  if (!material_scatter<false, DEFER, FEATS>(sc, rec, ray.d, r_out, albedo, skip_pdf, rng, pend))
     return true;
-  if (!skip_pdf && f.use_lights) { /* Book-3 mixture (raytracing.c:60-71) */
-    if (rng_f32(rng) < f.prob)
-      r_out = lights_rand<false>(sc, sc.lights_root, rec.p, rng);
+  if ((FEATS & FEAT_LIGHTS) && !skip_pdf && f.use_lights) { /* Book-3 mixture (raytracing.c:60-71) */
+    /* world.lights = one quad (Cornell box, Book 2 final): HittableList_rand's index draw (`u32 % 1`, hittable.c:101-107)
+     * is still made, HittableList_pdf's mean over one item is the item's pdf (hittable.c:89-100) */
+    if (rng_f32(rng) < f.prob) {
+#ifdef RTC_EXP_NO_ONE
+      if (false) {
+#else
+      if (sc.one_quad_light) {
+#endif
+        rng_u32(rng);
+        r_out = quad_rand(sc.light, rec.p, rng);
+      } else {
+        r_out = lights_rand<false>(sc, sc.lights_root, rec.p, rng);
+      }
+    }
     float scatter_pdf = material_scatter_pdf(sc, rec.material, rec.n, r_out);
     n_pdf++;
-    float sampling_pdf = (1.0f - f.prob) * scatter_pdf + f.prob * lights_pdf<false>(sc, sc.lights_root, rec.p, r_out);
+    const float light_pdf =
+#ifndef RTC_EXP_NO_ONE
+        sc.one_quad_light ? quad_pdf(sc.light, rec.p, r_out) :
+#endif
+        lights_pdf<false>(sc, sc.lights_root, rec.p, r_out);
+    float sampling_pdf = (1.0f - f.prob) * scatter_pdf + f.prob * light_pdf;
     albedo = v_scale(albedo, f_div(scatter_pdf, sampling_pdf));
   }
   beta = v_mul(beta, albedo);
@@ -168,7 +185,7 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * issues of a warp there): once plan.cta8/8 of the CTA's warps have finished the trip's traversal, the others suspend
  * theirs too (after at least one round, so every trip makes progress; warps without work do not count, so nobody is
  * suspended when few warps have work left). */
-template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME>
+template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS>
 __global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
@@ -185,7 +202,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   bool have_item = false, alive = false;
   /* the traversal state outlives a trip only in the RESUME kernels */
   uint32_t stack[TRACE_STACK - RTC_SMEM_STACK];
-  WalkerT<RTC_SMEM_STACK> wk;
+  WalkerT<RTC_SMEM_STACK, FEATS> wk;
   wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 1;
   /* dynamic shared memory: RTC_SMEM_STACK * BLOCK words (mega_variants) */
   wk.sbase = (uint32_t)__cvta_generic_to_shared(rtc_dyn_smem + threadIdx.x), wk.sstride = 4u * BLOCK;
@@ -206,7 +223,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   for (;; trip++) {
     /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
     if (!alive && !done) {
-      if (have_item && s == min(job.sample_begin + (chunk_id + 1) * plan.chunk, job.sample_begin + job.sample_count)) {
+      if (have_item && s == job.sample_begin + min(plan_chunk_begin(plan, chunk_id + 1), job.sample_count)) {
         /* chunk finished: one store per item */
         float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
                      ((size_t)pj * f.w + pi) * 3;
@@ -215,7 +232,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       }
       if (!have_item) {
         if (fetch_item(f, job, pi, pj, chunk_id)) {
-          s = job.sample_begin + chunk_id * plan.chunk;
+          s = job.sample_begin + plan_chunk_begin(plan, chunk_id);
           sum = v3(0, 0, 0);
           if (job.rng_mode == RT_RNG_PIXEL)
             rng_seed_pixel(rng, pi, pj);
@@ -282,7 +299,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     }
     if (alive && !(RESUME && walking)) {
       n_segments++;
-      if (sc.n_media)
+      if ((FEATS & FEAT_MEDIA) && sc.n_media)
         trace_media<false>(sc, ray, 1e-3f, th, rng);
     }
     if (LOCKSTEP)
@@ -295,7 +312,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     V3 L = v3(0, 0, 0);
     PendingTex pend;
     pend.tex = RT_NONE;
-    if (alive && !(RESUME && walking) && shade_segment<true>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
+    if (alive && !(RESUME && walking) &&
+        shade_segment<true, FEATS>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
       alive = false;
       s++;
       if (has_nan3(L)) {
@@ -308,7 +326,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     }
     /* Perlin albedos owed by this trip's hits: evaluated by the whole warp, one lookup after the other (the point is the
      * scattered ray's origin; a path that ended at max_depth owes one too, its throughput is not used again) */
-    if (sc.n_perlins)
+    if ((FEATS & FEAT_TEXTURES) && sc.n_perlins)
       perlin_settle_warp(sc, pend.tex, ray.o, beta);
   }
   /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
@@ -378,7 +396,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
         uint32_t pix = S.u(F_PIX, v);
         int pi = (int)(pix & 0xffffu), pj = (int)(pix >> 16), s = (int)S.u(F_S, v), chunk_id = (int)((meta >> 16) & 0xffu);
         if (meta & META_ITEM) {
-          const int s_end = min(job.sample_begin + (chunk_id + 1) * plan.chunk, s_last);
+          const int s_end = min(job.sample_begin + plan_chunk_begin(plan, chunk_id + 1), s_last);
           if (s == s_end) { /* chunk finished: one store per item */
             float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
                          ((size_t)pj * f.w + pi) * 3;
@@ -390,7 +408,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
         bool seeded = false;
         if (!(meta & META_ITEM)) {
           if (fetch_item(f, job, pi, pj, chunk_id)) {
-            s = job.sample_begin + chunk_id * plan.chunk;
+            s = job.sample_begin + plan_chunk_begin(plan, chunk_id);
             S.put(F_SX, v, v3(0, 0, 0));
             S.u(F_PIX, v) = (uint32_t)pi | ((uint32_t)pj << 16);
             if (job.rng_mode == RT_RNG_PIXEL) {
@@ -543,21 +561,28 @@ struct MegaVariant {
   MegaKernel fn;
   size_t smem;
   int block;
+  int feats; /* FEAT_* mask the kernel was instantiated with: it renders scenes whose mask is a subset */
 };
 #define STACK_SMEM(block) ((size_t)RTC_SMEM_STACK * (block) * sizeof(uint32_t)) /* WalkerT's shared-memory entries */
 static const MegaVariant mega_variants[] = {
-    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK}, /* first entry of an nv = its default */
-    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
-    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
-    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
-    {-1, 4, mega_render_kernel<4, 256, true, false>, STACK_SMEM(256), 256},
-    {-1, 2, mega_render_kernel<2, 512, true, false>, STACK_SMEM(512), 512},
-    {-1, 1, mega_render_kernel<1, 1024, true, false>, STACK_SMEM(1024), 1024},
+    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK, FEAT_ALL}, /* first entry of an nv = its default */
+    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK, FEAT_ALL},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
+    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
+    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
+    {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL},
+    {-1, 2, mega_render_kernel<2, 512, true, false, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL},
+    {-1, 1, mega_render_kernel<1, 1024, true, false, FEAT_ALL>, STACK_SMEM(1024), 1024, FEAT_ALL},
     /* nv = -2: lockstep CTAs whose trips do not wait for their longest rays (RESUME); nv = -3: the same, free-running */
-    {-2, 2, mega_render_kernel<2, 512, true, true>, STACK_SMEM(512), 512},
-    {-2, 4, mega_render_kernel<4, 256, true, true>, STACK_SMEM(256), 256},
-    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK},
+    {-2, 2, mega_render_kernel<2, 512, true, true, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL},
+    {-2, 4, mega_render_kernel<4, 256, true, true, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL},
+    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
+    /* LEAN instantiations: the same kernels without the code of what a scene does not contain.  FEATS = 0: spheres
+     * with solid-colour lambertian / metal / dielectric / emissive materials (scene 0, Book 1 final); quads + instances
+     * + light sampling, no media, no textures (the Cornell box). */
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
+    {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>, STACK_SMEM(256), 256,
+     FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS},
 };
 static int env_int(const char *name, int fallback) {
   const char *v = getenv(name);
@@ -569,37 +594,49 @@ static int env_int(const char *name, int fallback) {
  * +1.7 %).  RT_MEGA_NV (paths per lane: 0 = free-running register kernel, -1 = lockstep, -2 = lockstep + RESUME,
  * -3 = free-running + RESUME, 2/4 = warp ray queue) and RT_MEGA_MINB (CTAs per SM the
  * registers must allow) override; a combination that is not built falls back to the nv's first entry. */
-static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class) {
+static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class, int scene_feats) {
   int nv = env_int("RT_MEGA_NV", -99), minb = env_int("RT_MEGA_MINB", 0);
   if (nv == -99) {
     nv = scene_class == MEGA_SCENE_SPHERES ? 0 : scene_class == MEGA_SCENE_MEDIA ? -2 : -1;
     if (minb == 0 && nv < 0)
       minb = scene_class == MEGA_SCENE_MEDIA ? 2 : 4;
   }
+  if (env_int("RT_MEGA_LEAN", 1) == 0)
+    scene_feats = FEAT_ALL; /* A/B: only the kernels that carry everything */
   int want_nv = nv;
   /* the slot layout packs the pixel into 16+16 bits, the depth into 16 and the chunk into 8 */
   if (want_nv > 0 && (cam.img_width > 65535 || cam.img_height > 65535 || cam.max_depth > 65535 || n_chunks > 256))
     want_nv = 0;
   const int n = (int)(sizeof(mega_variants) / sizeof(mega_variants[0]));
-  for (int pass = 0; pass < 2; pass++)
-    for (int i = 0; i < n; i++)
-      if (mega_variants[i].nv == want_nv && (pass == 1 || mega_variants[i].minb == minb))
-        return &mega_variants[i];
+  /* among the kernels of that shape that cover the scene's features: the one that carries the least besides
+   * (pass 0: the requested register budget too; pass 1: any) */
+  for (int pass = 0; pass < 2; pass++) {
+    const MegaVariant *pick = nullptr;
+    for (int i = 0; i < n; i++) {
+      const MegaVariant &v = mega_variants[i];
+      if (v.nv != want_nv || (pass == 0 && v.minb != minb) || (scene_feats & ~v.feats) != 0)
+        continue;
+      if (!pick || __builtin_popcount(v.feats) < __builtin_popcount(pick->feats))
+        pick = &v;
+    }
+    if (pick)
+      return pick;
+  }
   for (int i = 0; i < n; i++)
-    if (mega_variants[i].nv == 0)
+    if (mega_variants[i].nv == 0 && mega_variants[i].feats == FEAT_ALL)
       return &mega_variants[i];
   return &mega_variants[0];
 }
 
 cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, int scene_class,
-                      MegaPlan *plan) {
+                      int scene_feats, MegaPlan *plan) {
   int sms = 0, per_sm = 0;
   cudaError_t err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (err != cudaSuccess)
     return err;
   /* chunking first (the variant depends on it only through a capacity check); the grid size is needed for the
    * chunk count, so take the default variant's occupancy for that estimate */
-  const MegaVariant *var = mega_variant(cam, 1, scene_class);
+  const MegaVariant *var = mega_variant(cam, 1, scene_class, scene_feats);
   if (var->smem > 48 * 1024) {
     err = cudaFuncSetAttribute(var->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)var->smem);
     if (err != cudaSuccess)
@@ -631,9 +668,27 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   }
   plan->chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->n_chunks = plan->chunk > 0 ? (sample_count + plan->chunk - 1) / plan->chunk : 1;
+  plan->n_big = plan->n_chunks, plan->small = plan->chunk;
+  /* Guided self-scheduling: work items are handed out chunk by chunk (all pixels' item 0, then all pixels' item 1,
+   * ...), and the kernel ends when the LAST items end -- with equal items the lanes finish up to one item apart
+   * (measured on 8 GPUs, 125 spp per rank in 12 items of 11 samples: 0.98 ms of a 29.5 ms kernel).  So the last
+   * ~8 % of a pixel's samples go out in items a quarter as long; the chunks are still summed in order. */
+  if (plan->n_chunks > 1 && plan->chunk >= 8 && env_int("RT_MEGA_GUIDED", 1) != 0) {
+    const int small = plan->chunk / 4 > 2 ? plan->chunk / 4 : 2;
+    int tail = (sample_count * 2 + 24) / 25; /* 8 % of the samples ... */
+    tail = ((tail + small - 1) / small) * small; /* ... in whole small items */
+    if (tail < sample_count) {
+      const int n_big = (sample_count - tail + plan->chunk - 1) / plan->chunk;
+      const int rest = sample_count - n_big * plan->chunk;
+      if (n_big >= 1 && rest > 0) {
+        plan->n_big = n_big, plan->small = small;
+        plan->n_chunks = n_big + (rest + small - 1) / small;
+      }
+    }
+  }
   plan->partial_bytes = plan->n_chunks > 1 ? (size_t)plan->n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
-  if (mega_variant(cam, plan->n_chunks, scene_class) != var) { /* capacity check failed: the register kernel */
-    var = mega_variant(cam, plan->n_chunks, scene_class);
+  if (mega_variant(cam, plan->n_chunks, scene_class, scene_feats) != var) { /* capacity check failed: the register kernel */
+    var = mega_variant(cam, plan->n_chunks, scene_class, scene_feats);
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, var->fn, var->block, var->smem);
     if (err != cudaSuccess)
       return err;

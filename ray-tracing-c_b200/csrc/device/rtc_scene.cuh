@@ -14,13 +14,16 @@
 /* ---- rebuilt acceleration structure (rtc_bvh.cpp builds it, rtc_mega.cu / rtc_wave.cu walk it) ---- */
 
 /* child / root reference: kind in bits 30-31, instance tag in bits 22-29, index in bits 0-21.
- * A leaf is ONE primitive (measured faster than 2 or 4 per leaf).  tag = 0: the primitive lives in the group's own
+ * A leaf is ONE primitive (measured faster than 2 or 4 per leaf) -- or one Box: the six quads of a Box_new list share
+ * one tight bound, so a tree over them only adds visits (Book 2 final: 400 boxes = 2 400 of its 2 401 quads); the leaf
+ * tests them one after the other in list order, exactly like HittableList_hit does (hittable.c:74-88).  tag = 0: the primitive lives in the group's own
  * frame; tag = k > 0: it lives under insts[k-1]'s transform chain -- the tree bounds it in the GROUP's frame and the
  * leaf test moves the ray into the primitive's frame with the reference's own operation sequence, so instances cost
  * no second traversal.  An inner reference is its node index (kind 0, tag 0). */
 #define REF_INNER 0u
 #define REF_SPHERES 1u
 #define REF_QUADS 2u
+#define REF_BOXES 3u /* SIX consecutive quads of mquads[] in the reference's list order: a Box (Box_new, hittable.c:246-264) */
 #define REF_EMPTY 0xFFFFFFFFu
 #define REF_INDEX_BITS 22
 #define REF_MAX_INDEX ((1u << REF_INDEX_BITS) - 1u)
@@ -76,6 +79,11 @@ struct __align__(16) MMedium {
   uint32_t material, node; /* phase function, node id */
   float neg_inv_density;
   uint32_t op_begin, op_count; /* transforms ABOVE the medium itself */
+  uint32_t in_list;            /* 1: reached through lists / transforms only (no BVHNode above it), so the reference
+                                  evaluates it at its list position with the running t_max -- reproduced draw for draw
+                                  (trace_media); 0: under a BVHNode, whose box test decides whether it is asked at all:
+                                  evaluated after the surfaces (same distribution, other draw count) */
+  uint32_t pad;
 };
 
 struct DScene {
@@ -100,6 +108,24 @@ struct DScene {
   const MMedium *media;
   uint32_t world_root, n_media;
   uint32_t n_perlins; /* 0: no Perlin texture in the scene (the megakernel skips the warp-wide lookups) */
+  /* world.lights is a list of exactly ONE quad (Cornell box, Book 2 final): the quad itself, here in the kernel's
+   * parameter space (constant bank, warp-uniform reads), so HittableList_pdf / _rand need no walk over the graph */
+  uint32_t feats;          /* FEAT_* mask of what the scene contains */
+  uint32_t one_quad_light; /* 1: `light` is valid */
+  rt_quad light;
+};
+
+/* What a scene CONTAINS, as a compile-time mask of the render kernels (template <int FEATS>): a kernel instantiated
+ * without a feature carries none of its code -- leaf tests, hit records, light sampling, media, texture lookups --
+ * which is registers, spills and instruction-cache footprint the sphere-only scenes (Book 1 final) then do not pay.
+ * rt_scene_create derives the scene's mask; mega_variant() only picks a lean kernel for a scene it covers. */
+enum {
+  FEAT_QUADS = 1,      /* quads / Box leaves in the rebuilt structure */
+  FEAT_INSTANCES = 2,  /* primitives under Translate / RotateY chains */
+  FEAT_LIGHTS = 4,     /* world.lights is not empty: the Book-3 mixture pdf may be evaluated */
+  FEAT_MEDIA = 8,      /* ConstantMedium items (and their isotropic phase functions) */
+  FEAT_TEXTURES = 16,  /* any texture that is not a solid colour (checker, image, Perlin) */
+  FEAT_ALL = 31,
 };
 
 /* material.h:10-18 plus the id of the node that produced the hit */

@@ -193,9 +193,11 @@ struct PendingTex {
 /* texture_value for an ALBEDO (a factor of the path throughput): a Perlin texture is not evaluated here -- 7 octaves x
  * 8 lattice corners on the one or two lanes of a warp that hit the marble sphere (ncu, Book 2 final: 8.4 % of all
  * warp instructions at 1.9 active lanes) -- but handed back as pending, with white as the factor for now. */
-template <bool EXACT, bool DEFER>
+template <bool EXACT, bool DEFER, int FEATS = FEAT_ALL>
 RTC_DEV V3 albedo_value(const DScene &sc, uint32_t id, float u, float v, V3 p, PendingTex &pend) {
   const rt_texture *t = &sc.textures[id];
+  if (!(FEATS & FEAT_TEXTURES)) /* every texture of the scene is a solid colour */
+    return v3(__ldg(&t->color[0]), __ldg(&t->color[1]), __ldg(&t->color[2]));
   const uint32_t kind = __ldg(&t->kind);
   if (kind == RT_TEX_SOLID)
     return v3(__ldg(&t->color[0]), __ldg(&t->color[1]), __ldg(&t->color[2]));
@@ -274,7 +276,7 @@ RTC_DEV V3 reflect(V3 incident, V3 normal) { /* material.c:45-47 */
 }
 
 /* material.c:103-120.  Returns false when the material does not scatter. */
-template <bool EXACT, bool DEFER>
+template <bool EXACT, bool DEFER, int FEATS = FEAT_ALL>
 RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_out, V3 &albedo, bool &skip_pdf,
                               Rng &g, PendingTex &pend) {
   const rt_material *m = &sc.materials[rec.material];
@@ -290,14 +292,14 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
     float sr2 = f_sqrt(r2);
     V3 local = v3(cs * sr2, sn * sr2, f_sqrt(1.0f - r2));
     r_out = basis_local(b, local);
-    albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
+    albedo = albedo_value<EXACT, DEFER, FEATS>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = false;
     return true;
   }
   case RT_MAT_METAL: { /* material.c:48-58: three draws per try even when fuzz == 0 */
     V3 mirrored = reflect(v_unit(r_in), rec.n);
     r_out = v_add(mirrored, v_scale(rng_unit_vector(g), __ldg(&m->param)));
-    albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
+    albedo = albedo_value<EXACT, DEFER, FEATS>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = true;
     if (v_dot(r_out, rec.n) < 0.0f)
       r_out = mirrored;
@@ -325,6 +327,10 @@ RTC_DEV bool material_scatter(const DScene &sc, const Hit &rec, V3 r_in, V3 &r_o
     return true;
   }
   case RT_MAT_ISOTROPIC: /* material.c:93-98 */
+    if (!(FEATS & FEAT_MEDIA)) { /* only ConstantMedium_init makes one (hittable.c:425-432) */
+      skip_pdf = true;
+      return false;
+    }
     r_out = rng_unit_vector(g);
     albedo = albedo_value<EXACT, DEFER>(sc, __ldg(&m->texture), rec.u, rec.v, rec.p, pend);
     skip_pdf = false;

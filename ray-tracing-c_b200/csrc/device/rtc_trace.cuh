@@ -50,7 +50,7 @@
  * stack costs one L1 wavefront per distinct depth in the warp and its lines are written back through L2 to DRAM);
  * deeper entries overflow to the lane's local array.  0: the whole stack in local memory. */
 #ifndef RTC_SMEM_STACK
-#define RTC_SMEM_STACK 8
+#define RTC_SMEM_STACK 0
 #endif
 #define PRIM_NONE 0xFFFFFFFFu
 #define PRIM_MEDIUM_KIND 3u     /* best_prim = MAKE_REF(3, 0, medium index) for a medium hit */
@@ -227,17 +227,18 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float a, f
 
 /* Intersects the ONE primitive of a leaf reference (sphere or quad) and keeps it if closer; ties as the reference.
  * `r` is the ray in the primitive's own frame, `inst` the instance that frame belongs to (RT_NONE: the group's). */
+template <int FEATS>
 RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float d_len2, float t_min, uint32_t inst,
                             TraceHit &best, uint32_t &best_node) {
   const uint32_t at = REF_INDEX(ref);
-  if (REF_KIND(ref) == REF_SPHERES) {
+  if (!(FEATS & FEAT_QUADS) || REF_KIND(ref) == REF_SPHERES) {
     const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[at]));
     float t;
     if (sphere_isect_closed(v3(s.x, s.y, s.z), s.w, r.o, r.d, d_len2, t_min, best.t, &t)) {
       if (t == best.t) {
         /* exact tie.  The reference's open interval (hittable.c:134-137) keeps the sphere it visited FIRST,
          * lets any quad win, and never accepts t == t_max itself; node ids are its visiting order. */
-        if (best.prim == PRIM_NONE || REF_KIND(best.prim) != REF_SPHERES)
+        if (best.prim == PRIM_NONE || ((FEATS & FEAT_QUADS) && REF_KIND(best.prim) != REF_SPHERES))
           return;
         if (__ldg(&sc.msph_meta[at].node) > __ldg(&sc.msph_meta[REF_INDEX(best.prim)].node))
           return;
@@ -287,7 +288,7 @@ RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float 
  * changes frame. */
 extern __shared__ __align__(16) uint32_t rtc_dyn_smem[]; /* dynamic shared memory of the render kernels */
 
-template <int SK> struct WalkerT {
+template <int SK, int FEATS = FEAT_ALL> struct WalkerT {
   uint32_t *stack;    /* TRACE_STACK entries owned by the caller (a separate local array, so that the scalar members
                          below stay in registers) */
   uint32_t sbase;     /* SK > 0: shared-window address of this lane's column of the CTA's stack (rtc_dyn_smem:
@@ -385,15 +386,28 @@ template <int SK> struct WalkerT {
   }
   /* one leaf: the primitive is tested in its own frame */
   template <class Outer> RTC_DEV void leaf_test(const DScene &sc, uint32_t ref, float t_min, Outer outer) {
-    const uint32_t tag = REF_TAG(ref);
+    const uint32_t tag = (FEATS & FEAT_INSTANCES) ? REF_TAG(ref) : 0u;
     Ray r = outer();
     float a = d_len2;
-    if (tag != 0u) {
+    if ((FEATS & FEAT_INSTANCES) && tag != 0u) {
       const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[tag - 1u]));
       r = chain_apply(sc, inst.x, inst.y, r);
       a = sv_len2(r.d);
     }
-    leaf_intersect(sc, ref, r, a, t_min, tag - 1u /* RT_NONE for tag 0 */, best, best_node);
+    /* a Box leaf is its six quads in list order, each against the running best (closed interval: a later face wins
+     * an exact tie, as in HittableList_hit); ONE transform of the ray serves all six */
+    uint32_t first = ref, count = 1u;
+#ifndef RTC_EXP_NO_BOX
+    if ((FEATS & FEAT_QUADS) && REF_KIND(ref) == REF_BOXES)
+      first = ref ^ ((REF_BOXES ^ REF_QUADS) << 30), count = 6u;
+#endif
+    if (FEATS & FEAT_QUADS) {
+#pragma unroll 1
+      for (uint32_t k = 0; k < count; k++)
+        leaf_intersect<FEATS>(sc, first + k, r, a, t_min, tag - 1u /* RT_NONE for tag 0 */, best, best_node);
+    } else {
+      leaf_intersect<FEATS>(sc, ref, r, a, t_min, RT_NONE, best, best_node);
+    }
   }
   template <class Outer> RTC_DEV void leaf(const DScene &sc, float t_min, Outer outer) {
     leaf_test(sc, cur, t_min, outer);
@@ -501,10 +515,59 @@ RTC_DEV bool sphere_boundary(V3 center, float radius, V3 o, V3 d, float &t_in, f
   return true;
 }
 
-/* ConstantMedium_hit (hittable.c:392-423) for every medium of the scene, after the surfaces: two boundary
- * queries, one draw when the clipped interval is not empty. */
+/* node id (= the reference's visiting order, DFS pre-order) of the object a TraceHit names */
+RTC_DEV uint32_t prim_node(const DScene &sc, uint32_t prim) {
+  const uint32_t idx = REF_INDEX(prim);
+  if (REF_KIND(prim) == REF_SPHERES)
+    return __ldg(&sc.msph_meta[idx].node);
+  if (REF_KIND(prim) == REF_QUADS)
+    return __float_as_uint(__ldg(&sc.mquads[idx].w_nod).w);
+  return sc.media[idx].node;
+}
+
+/* Closest surface hit in (t_min, t_max] among the primitives the reference visits BEFORE node `before` (node ids are
+ * its visiting order): the t_max a list item at that position is called with (HittableList_hit, hittable.c:74-88).
+ * +inf when there is none.  Rare (see trace_media), so out of line. */
+static __device__ __noinline__ float trace_early_call(const DScene &sc, const Ray &r, float t_min, float t_max,
+                                                       uint32_t before) {
+  uint32_t stack[TRACE_STACK];
+  Walker w;
+  w.stack = stack;
+  w.begin(sc.world_root, r, t_max);
+  auto outer = [&]() { return r; };
+  for (;;) {
+    while (w.at_inner())
+      w.visit<false>(sc, t_min);
+    if (w.done())
+      break;
+    /* (a Box leaf names its first quad; its six faces are one list, all before or all after `before`) */
+    if (prim_node(sc, REF_KIND(w.cur) == REF_BOXES ? w.cur ^ ((REF_BOXES ^ REF_QUADS) << 30) : w.cur) < before)
+      w.leaf_test(sc, w.cur, t_min, outer);
+    w.cur = w.pop();
+  }
+  return w.best.prim == PRIM_NONE ? RTC_INF : w.best.t;
+}
+
+/* ConstantMedium_hit (hittable.c:392-423) for every medium of the scene: two boundary queries, one draw when the
+ * clipped interval is not empty.
+ *
+ * The reference asks a medium AT ITS LIST POSITION: its t_max is the closest hit among the items BEFORE it, and the
+ * items after it are then tested against the medium's hit (HittableList_hit, hittable.c:74-88).  Here the surfaces
+ * are all traced first (`best` = the closest of ALL of them), so the same decisions -- and the same number of random
+ * draws -- are reproduced from that:
+ *   - the closest surface is an EARLIER item (node id below the medium's): it is the reference's t_max.  Exact.
+ *   - it is a LATER item at t_c: the reference's t_max T (closest earlier item) is only known to be >= t_c.  The draw
+ *     happens iff entry < min(exit, T): certain when entry < min(exit, t_c); when the later item lies in front of the
+ *     entry it takes one restricted query (is there an earlier item up to the entry?).  The accept test
+ *     travel <= (min(exit, T) - entry) * |d| is certain when exit <= t_c or travel fits below t_c already; and when
+ *     it is not, the outcome only matters if the medium's hit would beat the later item or another medium follows --
+ *     then T is computed (trace_early_call).  The later item finally meets the medium's hit as its t_max: it wins
+ *     iff t_c < t_m, or t_c == t_m for a quad (closed interval, hittable.c:194; spheres are open, :134-137).
+ * Media under a BVHNode (in_list == 0; none in the reference's scenes) are clipped against `best` as before: the
+ * node's box test decides in the reference whether they are asked at all, which a restricted query cannot tell. */
 template <bool EXACT>
 __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, float t_min, TraceHit &best, Rng &g) {
+  float early_med_t = RTC_INF; /* closest medium hit the reference has accepted so far (even one that a later item beat) */
   for (uint32_t m = 0; m < sc.n_media; m++) {
     const MMedium *med = &sc.media[m];
     Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
@@ -523,26 +586,57 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
       if (out.prim == PRIM_NONE)
         continue;
     }
-    float in_t = fmaxf(in.t, t_min), out_t = fminf(out.t, best.t);
-    if (in_t >= out_t)
+    const bool late = med->in_list != 0u && best.prim != PRIM_NONE && prim_node(sc, best.prim) > med->node;
+    float in_t = fmaxf(in.t, t_min);
+    float out_t = fminf(out.t, best.t); /* late: a LOWER bound of the reference's clipped exit min(out, T) */
+    bool sure = true;                   /* is out_t the reference's own value? */
+    if (late) {
+      if (in_t >= out.t)
+        continue; /* empty whatever T is: no draw on either side */
+      if (in_t >= out_t) {
+        /* the later item lies in front of the entry: the reference still draws unless an EARLIER item (or an earlier
+         * medium's hit) ends the interval before the entry */
+        if (fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
+          continue;
+        sure = false;
+      } else if (out.t > best.t) {
+        sure = false; /* T lies somewhere in [t_c, out] */
+      }
+    } else if (in_t >= out_t) {
       continue;
+    }
     in_t = in_t > 0.0f ? in_t : 0.0f;
     float ray_len = __fsqrt_rn(sv_len2(r.d));
-    float inside = s_mul(s_sub(out_t, in_t), ray_len);
     float travel = s_mul(med->neg_inv_density, m_log<EXACT>(rng_f32(g)));
-    if (travel > inside)
+    float t_m = s_add(in_t, s_div(travel, ray_len));
+    const bool beats = !late || t_m < best.t || (t_m == best.t && REF_KIND(best.prim) == REF_SPHERES);
+    if (!sure) {
+      /* travel <= (t_c - entry) * |d| is accepted whatever T >= t_c is (monotone rounding); otherwise only T tells */
+      if (in_t < out_t && travel <= s_mul(s_sub(out_t, in_t), ray_len)) {
+        sure = true;
+      } else {
+        if (!beats && m + 1 >= sc.n_media)
+          continue; /* the later item keeps the hit either way and nobody is asked after this medium */
+        out_t = fminf(out.t, fminf(trace_early_call(sc, world, t_min, RTC_INF, med->node), early_med_t));
+      }
+    }
+    if (travel > s_mul(s_sub(out_t, in_t), ray_len))
       continue;
-    best.t = s_add(in_t, s_div(travel, ray_len));
+    early_med_t = fminf(early_med_t, t_m);
+    if (!beats)
+      continue; /* the later item is tested with t_max = t_m and wins (hittable.c:80-84) */
+    best.t = t_m;
     best.prim = MAKE_REF(PRIM_MEDIUM_KIND, 0, m);
     best.inst = RT_NONE;
   }
 }
 
 /* Full hit record (world frame) of a TraceHit.  WANT_UV = false skips the sphere's atan2f/acosf. */
-template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &world, const TraceHit &h, Hit &rec) {
+template <bool EXACT, int FEATS = FEAT_ALL>
+RTC_DEV void trace_finalize(const DScene &sc, const Ray &world, const TraceHit &h, Hit &rec) {
   rec.t = h.t;
   const uint32_t kind = REF_KIND(h.prim), idx = REF_INDEX(h.prim);
-  if (kind == PRIM_MEDIUM_KIND) { /* only t, p, material (hittable.c:418-422) */
+  if ((FEATS & FEAT_MEDIA) && kind == PRIM_MEDIUM_KIND) { /* only t, p, material (hittable.c:418-422) */
     const MMedium *med = &sc.media[idx];
     Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
     rec.p = sv_at(r.o, r.d, h.t);
@@ -556,20 +650,20 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
   }
   Ray r = world;
   uint32_t op_begin = 0, op_count = 0;
-  if (h.inst != RT_NONE) {
+  if ((FEATS & FEAT_INSTANCES) && h.inst != RT_NONE) {
     const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[h.inst]));
     op_begin = inst.x, op_count = inst.y;
     r = chain_apply_call(sc, op_begin, op_count, world);
   }
-  if (kind == REF_SPHERES) {
+  if (!(FEATS & FEAT_QUADS) || kind == REF_SPHERES) {
     const float4 s = __ldg(reinterpret_cast<const float4 *>(&sc.msph[idx]));
     const uint2 meta = __ldg(reinterpret_cast<const uint2 *>(&sc.msph_meta[idx]));
     rec.material = meta.x;
     rec.node = meta.y;
     rec.u = rec.v = 0.0f;
-    const uint32_t tex = __ldg(&sc.materials[meta.x].texture);
     sphere_record<EXACT, false>(v3(s.x, s.y, s.z), s.w, r.o, r.d, h.t, rec);
-    if (EXACT || texture_needs_uv(sc, tex)) /* (u, v) cost an atan2 and an acos: only for textures that read them */
+    /* (u, v) cost an atan2 and an acos: only for textures that read them */
+    if (EXACT || ((FEATS & FEAT_TEXTURES) && texture_needs_uv(sc, __ldg(&sc.materials[meta.x].texture))))
       sphere_uv<EXACT>(rec.front ? rec.n : v_neg(rec.n), rec);
   } else {
     const MQuad *q = &sc.mquads[idx];
@@ -585,7 +679,7 @@ template <bool EXACT> RTC_DEV void trace_finalize(const DScene &sc, const Ray &w
     rec.front = sv_dot(r.d, nrm) < 0.0f;
     rec.n = rec.front ? nrm : v_neg(nrm);
   }
-  if (op_count)
+  if ((FEATS & FEAT_INSTANCES) && op_count)
     chain_unapply_call(sc, op_begin, op_count, rec.p, rec.n);
 }
 

@@ -90,8 +90,8 @@ __device__ __noinline__ unsigned wave_regenerate(const RenderJob &job, const Meg
         if (pi >= w || pj >= h)
           continue; /* padding of the last tile column / row */
         it.x = (uint32_t)(pj * w + pi);
-        it.y = (uint32_t)(job.sample_begin + (int)c * plan.chunk);
-        it.z = (uint32_t)min((int)it.y + plan.chunk, job.sample_begin + job.sample_count);
+        it.y = (uint32_t)(job.sample_begin + plan_chunk_begin(plan, (int)c));
+        it.z = (uint32_t)(job.sample_begin + min(plan_chunk_begin(plan, (int)c + 1), job.sample_count));
         it.w = c;
         sum = make_float4(0, 0, 0, 0);
         have = true;
@@ -348,6 +348,7 @@ cudaError_t wave_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
   plan->mega.blocks = 0, plan->mega.threads = 0, plan->mega.minb = 0, plan->mega.nv = 0;
   plan->mega.chunk = (sample_count + n_chunks - 1) / n_chunks;
   plan->mega.n_chunks = (sample_count + plan->mega.chunk - 1) / plan->mega.chunk;
+  plan->mega.n_big = plan->mega.n_chunks, plan->mega.small = plan->mega.chunk; /* equal items */
   plan->mega.partial_bytes =
       plan->mega.n_chunks > 1 ? (size_t)plan->mega.n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
   /* pool: many full waves of every SM per launch (the two launches of an iteration cost a few microseconds of

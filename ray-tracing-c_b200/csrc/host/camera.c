@@ -4,7 +4,7 @@
  *   World_init      /root/reference/src/raytracing.c:8-11
  *   Camera_init     /root/reference/src/raytracing.c:13-37  (kept on the host with glibc tanf; the device only sees
  *                   the derived vectors, so camera rays are bit-identical to the reference's)
- *   Camera_render   /root/reference/src/raytracing.c:86-135 -- here: flatten -> rt_scene_create -> rt_render
+ *   Camera_render   /root/reference/src/raytracing.c:86-135 -- here: flatten -> rt_scene_acquire -> rt_render
  *                   (sm_100a kernels) -> rgb8 back in the caller's buffer.  No pixel is computed on the host.
  *
  * Environment knobs read by Camera_render (the signature has no room for options):
@@ -71,11 +71,13 @@ int rtc_camera_render_opts(const Camera *camera, const World *world, const rt_op
 
   int status;
   if (n_gpus <= 1) {
+    /* the uploaded scene comes from (and goes back to) the library's cache, keyed by the description's content: a
+     * second Camera_render on the same World skips the BVH build and the upload */
     rt_scene *scene = NULL;
-    status = rt_scene_create(&desc, -1, &scene);
+    status = rt_scene_acquire(&desc, -1, &scene);
     if (status == RT_OK) {
       status = rt_render(scene, &cam, opts, radiance_sum, rgb8, stats);
-      rt_scene_destroy(scene);
+      rt_scene_release(scene);
     }
   } else {
     status = rt_render_multi(&desc, &cam, opts, n_gpus, radiance_sum, rgb8, stats);

@@ -21,7 +21,8 @@ REPO_ROOT = PKG_DIR.parent
 
 # every symbol include/rtc_b200.h declares (tests check the .so exports each one)
 B200_SYMBOLS = [
-    "rt_last_error", "rt_abi_version", "rt_device_count", "rt_scene_inspect", "rt_scene_create", "rt_scene_destroy", "rt_render",
+    "rt_last_error", "rt_abi_version", "rt_device_count", "rt_scene_inspect", "rt_scene_create", "rt_scene_destroy",
+    "rt_scene_acquire", "rt_scene_release", "rt_shutdown", "rt_render",
     "rt_render_device", "rt_render_device_stats", "rt_tonemap_device", "rt_hit_batch", "rt_render_multi",
     "rt_fp32_peak",
 ]
@@ -83,6 +84,10 @@ def b200() -> C.CDLL:
     lib.rt_device_count.restype = i32
     lib.rt_scene_create.argtypes = [C.POINTER(abi.rt_scene_desc), i32, C.POINTER(vp)]
     lib.rt_scene_destroy.argtypes = [vp]
+    lib.rt_scene_acquire.argtypes = [C.POINTER(abi.rt_scene_desc), i32, C.POINTER(vp)]
+    lib.rt_scene_release.argtypes = [vp]
+    lib.rt_scene_release.restype = None
+    lib.rt_shutdown.restype = None
     lib.rt_scene_inspect.argtypes = [C.POINTER(abi.rt_scene_desc), C.POINTER(abi.rt_scene_info)]
     lib.rt_scene_destroy.restype = None
     lib.rt_render.argtypes = [vp, C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts), vp, vp, C.POINTER(abi.rt_stats)]

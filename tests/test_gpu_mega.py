@@ -73,10 +73,10 @@ def test_hit_parity_second_bounce_on_bvh_scenes(rtc, oracle, gpu_scene):
 
 
 def test_hit_parity_with_media(rtc, oracle, golden, gpu_scene):
-    """Scene 7.  Surfaces: bit-identical t and identical ids wherever neither side reports a medium.  Media are
-    evaluated AFTER the surfaces here and BETWEEN them in the reference (list order), so a ray can draw a different
-    number of randoms; the hit decision is distributionally the same (memoryless free path) -- the fraction of rays
-    ending in a medium must match the oracle's within sampling error."""
+    """Scene 7 (two ConstantMedium items in the world list).  The rebuilt structure traces all surfaces first and
+    then reproduces the reference's in-list evaluation of the media from that (trace_media, rtc_trace.cuh): the same
+    hit, the same hit distance bits and the SAME NUMBER OF RANDOM DRAWS on every ray -- so ids, t and the advanced
+    PCG32 states are compared for equality, media included (/root/reference/src/hittable.c:74-88,392-423)."""
     sess, desc, scene = gpu_scene(7)
     origins, dirs = _batch(sess, desc, golden(7), n=150_000)
     rng = raygen.rng_states(len(origins), seed=203)
@@ -84,18 +84,21 @@ def test_hit_parity_with_media(rtc, oracle, golden, gpu_scene):
     got = scene.hit_batch(origins, dirs, rng=rng, kernel="mega")
     is_medium = desc.nodes["kind"] == rtc.abi.NODE_MEDIUM
     med_w = (want["node"] != rtc.abi.RT_NONE) & is_medium[np.minimum(want["node"], len(is_medium) - 1)]
-    med_g = (got["node"] != rtc.abi.RT_NONE) & is_medium[np.minimum(got["node"], len(is_medium) - 1)]
-    surf = ~med_w & ~med_g
-    assert surf.mean() > 0.5
-    assert same_bits(got["t"][surf], want["t"][surf]).all()
-    assert np.array_equal(got["node"][surf], want["node"][surf])
-    n = len(origins)
-    p_w, p_g = med_w.mean(), med_g.mean()
-    assert abs(p_w - p_g) < 4 * np.sqrt(max(p_w, 1e-4) / n) + 1e-3, (p_w, p_g)
-    # most rays take the same draws on both sides: identical medium hits, bit for bit, are the norm
-    same = med_w & med_g & (got["node"] == want["node"])
-    assert same.sum() > 0.8 * med_w.sum()
-    assert (ulp_distance(got["t"][same], want["t"][same]) <= 64).mean() > 0.9
+    assert 0.02 < med_w.mean() < 0.9  # the batch does exercise the media
+    drew = want["rng"][:, 0] != rng[:, 0]
+    assert drew.mean() > 0.5          # ... and most rays draw (the r = 5000 fog ball encloses the scene)
+    assert np.array_equal(got["rng"], want["rng"])
+    assert np.array_equal(got["node"], want["node"])
+    assert same_bits(got["t"], want["t"]).all()
+    hit = want["node"] != rtc.abi.RT_NONE
+    assert same_bits(got["p"][hit], want["p"][hit]).all()
+    assert np.array_equal(got["material"], want["material"])
+    # rays whose closest surface is a LATER list item than a medium they also cross: the case the restricted
+    # queries of trace_media exist for -- present in the batch, not just in theory
+    node = want["node"].astype(np.int64)
+    med_ids = np.flatnonzero(is_medium)
+    later_surface = hit & ~med_w & (node > med_ids.min())
+    assert (later_surface & drew).sum() > 100
 
 
 def _rmse(a, b):
@@ -220,6 +223,37 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
         assert same_bits(rad, rad_ref).all(), (nv, minb, thr8, resume8)
         assert np.array_equal(rgb, rgb_ref)
         assert st["segments"] == st_ref["segments"] and st["samples"] == st_ref["samples"]
+    # the LEAN instantiations (kernels without the code of features the scene lacks) against the full ones, the
+    # guided item sizes against equal ones (same chunk boundaries are not kept: compare with a looser bar), and the
+    # one-quad light fast path against the generic walk over world.lights
+    for name in ("RT_MEGA_NV", "RT_MEGA_MINB", "RT_MEGA_THR8", "RT_MEGA_RESUME8", "RT_MEGA_CTA8"):
+        monkeypatch.delenv(name, raising=False)
+    rgb_d, rad_d, st_d = scene.render(sess.camera, opts)
+    monkeypatch.setenv("RT_MEGA_LEAN", "0")
+    rgb, rad, st = scene.render(sess.camera, opts)
+    assert same_bits(rad, rad_d).all() and st["segments"] == st_d["segments"]
+    monkeypatch.delenv("RT_MEGA_LEAN")
+
+
+@pytest.mark.parametrize("scene_id", [5, 6, 7])
+def test_scene_build_options_agree_bit_for_bit(rtc, scene_factory, scene_id, monkeypatch):
+    """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, and the one-quad-light fast
+    path against the generic walk over world.lights: other structure, other code, the same hits, the same draws --
+    the float radiance must be identical bit for bit."""
+    sess, desc = scene_factory(scene_id, 96, 32)
+    opts = rtc.make_opts(kernel="mega", rng="sample")
+    results = []
+    for env in ({}, {"RT_BVH_BOXES": "0"}, {"RT_ONE_LIGHT_OFF": "1"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        scene = rtc.Scene(desc)
+        results.append(scene.render(sess.camera, opts))
+        scene.close()
+        for k in env:
+            monkeypatch.delenv(k)
+    for rgb, rad, st in results[1:]:
+        assert same_bits(rad, results[0][1]).all()
+        assert st["segments"] == results[0][2]["segments"]
 
 
 def test_sample_ranges_add_up(rtc, gpu_scene):
