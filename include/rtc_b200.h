@@ -271,6 +271,9 @@ int rt_render_device_stats(rt_scene *scene, void *cuda_stream, rt_stats *stats);
 
 /* rgb8_dev[i] = (int)(256 * clamp(sqrtf(sum[i] / spp), 0, 0.999)), NaN -> 0   (raytracing.c:127-131). */
 int rt_tonemap_device(const float *radiance_sum_dev, size_t n_values, int spp, uint8_t *rgb8_dev, void *cuda_stream);
+/* The same epilogue through HOST buffers (upload, kernel, download; blocking): for a caller that summed the float
+ * radiance of several sample-range passes itself (rtc_main --passes / --checkpoint). */
+int rt_tonemap(const float *radiance_sum, size_t n_values, int spp, uint8_t *rgb8);
 
 /* Closest hit of n rays against world.objects, all HOST arrays, [t_min, t_max] as in the vtable slot.
  *   origins, dirs : float[n][3]

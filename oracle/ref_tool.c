@@ -15,6 +15,10 @@
  *                                                                           reference's own timer, src/main.c:334-338)
  *   ref_tool flatten <scene> <out.blob>                                     rt_scene_desc of the reference's graph
  *   ref_tool hits    <scene> <rays.bin> <out.bin>                           world.objects.hit() on a ray batch
+ *   ref_tool tiff    0 <width> <height> <channels> <out.tiff>               the reference's write_tiff (src/tiff.c:15-49)
+ *                                                                           on the byte pattern (7 i + 3) mod 251
+ *   ref_tool image   0 <file> <out.rgb8>                                    the reference's Image_init (src/texture.c:38-42:
+ *                                                                           stbi_load, 3 channels) -> "w h\n" + RGB8 bytes
  *
  * Scenes 3 and 7 load "earthmap.jpg" from the working directory; the tool first writes the synthetic image there
  * as a binary PPM under that name (stb_image sniffs content, not the extension).
@@ -95,6 +99,28 @@ int main(int argc, char **argv) {
     return 2;
   }
   const char *cmd = argv[1];
+  if (strcmp(cmd, "tiff") == 0 && argc == 7) {
+    int w = atoi(argv[3]), h = atoi(argv[4]), c = atoi(argv[5]);
+    size_t n = (size_t)w * h * c;
+    uint8_t *px = malloc(n);
+    for (size_t i = 0; i < n; i++)
+      px[i] = (uint8_t)((7 * i + 3) % 251);
+    FILE *f = fopen(argv[6], "wb");
+    assert(f != NULL);
+    int rc = write_tiff(f, w, h, c, px);
+    fclose(f);
+    return rc;
+  }
+  if (strcmp(cmd, "image") == 0 && argc == 5) {
+    Image im;
+    Image_init(&im, argv[3]); /* asserts when stb cannot decode the file, like the reference */
+    FILE *f = fopen(argv[4], "wb");
+    assert(f != NULL);
+    fprintf(f, "%d %d\n", im.width, im.height);
+    fwrite(im.buffer, 1, (size_t)im.width * im.height * 3, f);
+    fclose(f);
+    return 0;
+  }
   int scene = atoi(argv[2]);
   World world = {0};
   Camera camera;

@@ -445,6 +445,32 @@ extern "C" int rt_tonemap_device(const float *radiance_sum_dev, size_t n_values,
   return RT_OK;
 }
 
+/* the same through HOST buffers (upload, kernel, download): for callers that accumulated a float sum themselves,
+ * e.g. the progressive / checkpointed passes of rtc_main -- the epilogue still runs on the device */
+extern "C" int rt_tonemap(const float *radiance_sum, size_t n_values, int spp, uint8_t *rgb8) {
+  if (!radiance_sum || !rgb8 || spp <= 0)
+    return fail(RT_ERR_INVALID, "rt_tonemap: bad argument");
+  if (rt_device_count() <= 0)
+    return fail(RT_ERR_NO_DEVICE, "rt_tonemap: no CUDA device (this library does not compute on the host)");
+  if (n_values == 0)
+    return RT_OK;
+  float *sum_dev = nullptr;
+  uint8_t *rgb_dev = nullptr;
+  CUDA_TRY(dev_alloc((void **)&sum_dev, n_values * sizeof(float)));
+  cudaError_t err = dev_alloc((void **)&rgb_dev, n_values);
+  if (err == cudaSuccess)
+    err = cudaMemcpy(sum_dev, radiance_sum, n_values * sizeof(float), cudaMemcpyHostToDevice);
+  int rc = RT_OK;
+  if (err == cudaSuccess)
+    rc = rt_tonemap_device(sum_dev, n_values, spp, rgb_dev, nullptr);
+  if (err == cudaSuccess && rc == RT_OK)
+    err = cudaMemcpy(rgb8, rgb_dev, n_values, cudaMemcpyDeviceToHost);
+  dev_free(sum_dev), dev_free(rgb_dev);
+  if (err != cudaSuccess)
+    return fail(RT_ERR_CUDA, "rt_tonemap: %s", cudaGetErrorString(err));
+  return rc;
+}
+
 /* ------------------------------------------------------------------ render ------------------------------- */
 
 static int resolve_range(const rt_camera *cam, const rt_opts *opts, int *begin, int *count) {
@@ -690,9 +716,17 @@ NcclApi &nccl_api() {
   const char *off = getenv("RT_MULTI_NCCL");
   if (off && off[0] == '0')
     return api;
-  api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  /* Which libnccl.so.2: (1) RT_NCCL_LIB, a path given by the host program (the Python mirror points it at the copy
+   * PyTorch bundles, so that a later `import torch` in the same process finds the SAME library under that soname and
+   * not an older system one -- two NCCL versions cannot share a process); (2) one that is already mapped; (3) the
+   * system's.  RTLD_LOCAL: nothing else in the process should bind to it because of us. */
+  const char *path = getenv("RT_NCCL_LIB");
+  if (path && *path)
+    api.handle = dlopen(path, RTLD_NOW | RTLD_LOCAL);
   if (!api.handle)
-    api.handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+  if (!api.handle)
+    api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
   if (!api.handle)
     return api;
 #define NCCL_SYM(field, name) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, name))
@@ -751,8 +785,8 @@ int multi_setup(int n_gpus) {
     CUDA_TRY(cudaStreamCreateWithFlags(&m.streams[g], cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreateWithFlags(&m.done[g], cudaEventDisableTiming));
   }
-  NcclApi &api = nccl_api();
-  if (api.ok) {
+  if (n_gpus > 1 && nccl_api().ok) { /* (one GPU exchanges nothing: NCCL is not even loaded) */
+    NcclApi &api = nccl_api();
     std::vector<int> devs(n_gpus);
     for (int g = 0; g < n_gpus; g++)
       devs[g] = g;

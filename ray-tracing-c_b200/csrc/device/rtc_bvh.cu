@@ -238,7 +238,7 @@ static float env_float(const char *name, float fallback) {
 static const float kCostNode = 1.0f, kCostSphere = env_float("RT_BVH_COST_SPHERE", 0.8f),
                    kCostQuad = env_float("RT_BVH_COST_QUAD", 1.4f), kCostBox = env_float("RT_BVH_COST_BOX", 4.0f);
 /* RT_BVH_BOXES=0: every quad its own leaf (the round-1 structure), for A/B measurements; read at every build */
-static bool box_leaves_enabled() { return env_float("RT_BVH_BOXES", 1.0f) != 0.0f; }
+static bool box_leaves_enabled() { return env_float("RT_BVH_BOXES", 0.0f) != 0.0f; }
 
 struct Builder {
   const rt_scene_desc &d;

@@ -581,6 +581,8 @@ static const MegaVariant mega_variants[] = {
      * with solid-colour lambertian / metal / dielectric / emissive materials (scene 0, Book 1 final); quads + instances
      * + light sampling, no media, no textures (the Cornell box). */
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
+    {0, 10, mega_render_kernel<10, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
+    {0, 12, mega_render_kernel<12, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
     {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>, STACK_SMEM(256), 256,
      FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS},
 };

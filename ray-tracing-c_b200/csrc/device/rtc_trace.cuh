@@ -37,6 +37,9 @@
 #ifndef RTC_MEDIA_FAST
 #define RTC_MEDIA_FAST 1
 #endif
+#ifndef RTC_MEDIA_INLIST
+#define RTC_MEDIA_INLIST 1 /* 0: media clipped against the closest surface whatever its list position (round 1) */
+#endif
 #ifndef RTC_POSTPONE
 #define RTC_POSTPONE 1 /* 1: kernels of <= 256 threads park the first leaf of a round and keep descending; 2: all; 0: none */
 #endif
@@ -200,6 +203,26 @@ RTC_DEV float s_div_z(float x, float y) {
   return s_div(x, y);
 }
 
+/* Is the IEEE quotient num / den CERTAINLY outside [lo, hi]?  Decided from the one-MUFU reciprocal: its product with
+ * num is within 2.4e-7 (relative) of the correctly rounded quotient, the margin asked for is 1e-6 -- so a candidate
+ * that is rejected here would have been rejected by the exact comparison too, and the ~10-instruction IEEE division
+ * (plus its slow path) is only paid by candidates near or inside the interval.  Most leaf candidates are not: a plane
+ * hit behind the origin or beyond the best hit so far.  den must be a normal, non-zero number. */
+#ifndef RTC_DIV_PRETEST
+#define RTC_DIV_PRETEST 1
+#endif
+RTC_DEV bool quotient_outside(float num, float den, float lo, float hi) {
+#if RTC_DIV_PRETEST
+  float inv;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(den));
+  const float q = num * inv;
+  /* (lo = -inf or hi = +inf: never outside on that side; NaN compares false: the exact path decides) */
+  return q < lo - 1e-6f * fabsf(lo) - 1e-30f || q > hi + 1e-6f * fabsf(hi) + 1e-30f;
+#else
+  return false;
+#endif
+}
+
 /* sphere_isect with t_max INCLUDED, so that the traversal can see exact ties and resolve them like the reference.
  * `a` = |d|^2 in the reference's operation order (sv_len2), computed once per ray frame by the caller.  The far root
  * is only computed when the near one is behind t_min: both are monotone in the same rounded operands
@@ -213,7 +236,11 @@ RTC_DEV bool sphere_isect_closed(V3 center, float radius, V3 o, V3 d, float a, f
   if (disc < 0.0f)
     return false;
   float sq = __fsqrt_rn(disc);
-  float root = s_div_z(s_sub(-b, sq), a);
+  const float near_num = s_sub(-b, sq);
+  /* the near root certainly beyond t_max: a miss whatever the far root is (it is not smaller) */
+  if (quotient_outside(near_num, a, -RTC_INF, t_max))
+    return false;
+  float root = s_div_z(near_num, a);
   if (root > t_max)
     return false;
   if (root <= t_min) {
@@ -255,7 +282,10 @@ RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float 
     float denom = sv_dot(nrm, r.d);
     if (fabsf(denom) < 1e-8f)
       return;
-    float tt = s_div_z(s_sub(n_D.w, sv_dot(nrm, r.o)), denom);
+    const float num = s_sub(n_D.w, sv_dot(nrm, r.o));
+    if (quotient_outside(num, denom, t_min, best.t))
+      return;
+    float tt = s_div_z(num, denom);
     if (tt < t_min || tt > best.t)
       return;
     const float4 q_mat = __ldg(&q->q_mat), w_nod = __ldg(&q->w_nod), u_ar = __ldg(&q->u_ar), v_ = __ldg(&q->v_);
@@ -586,45 +616,58 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
       if (out.prim == PRIM_NONE)
         continue;
     }
-    const bool late = med->in_list != 0u && best.prim != PRIM_NONE && prim_node(sc, best.prim) > med->node;
+    /* is the closest surface a LATER list item than this medium?  Asked lazily: it costs a dependent load of the
+     * primitive's node id, and the common outcomes below do not depend on it. */
+    auto is_late = [&]() {
+      return RTC_MEDIA_INLIST && med->in_list != 0u && best.prim != PRIM_NONE && prim_node(sc, best.prim) > med->node;
+    };
     float in_t = fmaxf(in.t, t_min);
-    float out_t = fminf(out.t, best.t); /* late: a LOWER bound of the reference's clipped exit min(out, T) */
-    bool sure = true;                   /* is out_t the reference's own value? */
-    if (late) {
-      if (in_t >= out.t)
-        continue; /* empty whatever T is: no draw on either side */
-      if (in_t >= out_t) {
-        /* the later item lies in front of the entry: the reference still draws unless an EARLIER item (or an earlier
-         * medium's hit) ends the interval before the entry */
-        if (fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
-          continue;
-        sure = false;
-      } else if (out.t > best.t) {
-        sure = false; /* T lies somewhere in [t_c, out] */
-      }
-    } else if (in_t >= out_t) {
-      continue;
+    float out_t = fminf(out.t, best.t); /* the reference's clipped exit if `best` is an earlier item, else a LOWER bound */
+    if (in_t >= out.t)
+      continue; /* empty whatever the reference's t_max is: no draw on either side */
+    bool late = false, late_known = false, sure = true;
+    if (in_t >= out_t) {
+      /* `best` ends the interval before the entry.  An earlier item: no draw.  A later item: the reference still
+       * draws, unless an EARLIER item (or an earlier medium's hit) ends the interval before the entry too */
+      late = is_late(), late_known = true;
+      if (!late || fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
+        continue;
+      sure = false;
     }
     in_t = in_t > 0.0f ? in_t : 0.0f;
     float ray_len = __fsqrt_rn(sv_len2(r.d));
     float travel = s_mul(med->neg_inv_density, m_log<EXACT>(rng_f32(g)));
     float t_m = s_add(in_t, s_div(travel, ray_len));
-    const bool beats = !late || t_m < best.t || (t_m == best.t && REF_KIND(best.prim) == REF_SPHERES);
-    if (!sure) {
-      /* travel <= (t_c - entry) * |d| is accepted whatever T >= t_c is (monotone rounding); otherwise only T tells */
-      if (in_t < out_t && travel <= s_mul(s_sub(out_t, in_t), ray_len)) {
-        sure = true;
-      } else {
-        if (!beats && m + 1 >= sc.n_media)
-          continue; /* the later item keeps the hit either way and nobody is asked after this medium */
-        out_t = fminf(out.t, fminf(trace_early_call(sc, world, t_min, RTC_INF, med->node), early_med_t));
-      }
+    if (sure && travel > s_mul(s_sub(out_t, in_t), ray_len)) {
+      /* does not fit below `best`: rejected if best is an earlier item (or the boundary's own exit); if it is a later
+       * item at t_c < exit the reference's t_max lies in [t_c, exit] and may still admit the hit */
+      if (out.t <= best.t)
+        continue;
+      if (t_m > best.t && m + 1 >= sc.n_media)
+        continue; /* `best` keeps the hit either way, and nobody is asked after this medium */
+      late = is_late(), late_known = true;
+      if (!late)
+        continue;
+      sure = false;
     }
-    if (travel > s_mul(s_sub(out_t, in_t), ray_len))
-      continue;
+    if (!sure) {
+      const bool beats = t_m < best.t || (t_m == best.t && REF_KIND(best.prim) == REF_SPHERES);
+      if (!beats && m + 1 >= sc.n_media)
+        continue; /* the later item keeps the hit either way and nobody is asked after this medium */
+      out_t = fminf(out.t, fminf(trace_early_call(sc, world, t_min, RTC_INF, med->node), early_med_t));
+      if (travel > s_mul(s_sub(out_t, in_t), ray_len))
+        continue;
+    }
+    /* accepted by the reference */
     early_med_t = fminf(early_med_t, t_m);
-    if (!beats)
-      continue; /* the later item is tested with t_max = t_m and wins (hittable.c:80-84) */
+    if (t_m >= best.t && best.prim != PRIM_NONE) {
+      /* (only by rounding, or behind a later item) an earlier item is overridden by the medium's hit; a later item is
+       * tested with t_max = t_m afterwards and wins unless it is a sphere at exactly t_m (hittable.c:80-84, 134-137, 194) */
+      if (!late_known)
+        late = is_late();
+      if (late && !(t_m == best.t && REF_KIND(best.prim) == REF_SPHERES))
+        continue;
+    }
     best.t = t_m;
     best.prim = MAKE_REF(PRIM_MEDIUM_KIND, 0, m);
     best.inst = RT_NONE;

@@ -114,6 +114,14 @@ void Camera_render(const Camera *camera, const World *world, uint8_t *buffer) {
   fprintf(stderr, "\rScanlines remaining: %d", camera->img_height); /* the reference's progress line, coarse */
   rt_stats stats;
   int status = rtc_camera_render_opts(camera, world, &opts, n_gpus, buffer, NULL, &stats);
+  if (status == RT_ERR_UNSUPPORTED && opts.kernel != RT_KERNEL_EXACT) {
+    /* the rebuilt structure has limits the reference does not (255 distinct Translate/RotateY chains, 48 levels of
+     * BVH): the reference-order kernel has neither, so the frame is still rendered, only slower */
+    fprintf(stderr, "\nrtc_b200: %s -- rendering with the reference-order kernel (RT_KERNEL=exact) instead\n",
+            rt_last_error());
+    opts.kernel = RT_KERNEL_EXACT;
+    status = rtc_camera_render_opts(camera, world, &opts, n_gpus, buffer, NULL, &stats);
+  }
   if (status != RT_OK) {
     /* the reference's error convention is assert -> abort; there is no CPU fallback to hide behind */
     fprintf(stderr, "\nrtc_b200: render failed (%d): %s\n", status, rt_last_error());

@@ -23,7 +23,7 @@ REPO_ROOT = PKG_DIR.parent
 B200_SYMBOLS = [
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_scene_inspect", "rt_scene_create", "rt_scene_destroy",
     "rt_scene_acquire", "rt_scene_release", "rt_shutdown", "rt_render",
-    "rt_render_device", "rt_render_device_stats", "rt_tonemap_device", "rt_hit_batch", "rt_render_multi",
+    "rt_render_device", "rt_render_device_stats", "rt_tonemap_device", "rt_tonemap", "rt_hit_batch", "rt_render_multi",
     "rt_fp32_peak",
 ]
 HOST_SYMBOLS = [
@@ -72,11 +72,31 @@ def _load(name: str) -> C.CDLL:
     return C.CDLL(str(path), mode=C.RTLD_GLOBAL)
 
 
+def _point_at_bundled_nccl() -> None:
+    """rt_render_multi dlopens NCCL at its first multi-GPU call.  In a Python process that may import torch LATER the
+    library under the soname libnccl.so.2 must be the one torch was built against (the wheel bundles it under
+    nvidia/nccl/lib), not an older system copy: tell the C side where it is (RT_NCCL_LIB), without importing torch."""
+    if os.environ.get("RT_NCCL_LIB"):
+        return
+    import importlib.util
+
+    try:
+        spec = importlib.util.find_spec("nvidia")
+    except (ImportError, ValueError):
+        spec = None
+    for base in (spec.submodule_search_locations if spec and spec.submodule_search_locations else []):
+        cand = Path(base) / "nccl" / "lib" / "libnccl.so.2"
+        if cand.exists():
+            os.environ["RT_NCCL_LIB"] = str(cand)
+            return
+
+
 def b200() -> C.CDLL:
     """librtc_b200.so with argtypes declared."""
     global _b200
     if _b200 is not None:
         return _b200
+    _point_at_bundled_nccl()
     lib = _load("librtc_b200.so")
     vp, u32, i32, sz, f32 = C.c_void_p, C.c_uint32, C.c_int, C.c_size_t, C.c_float
     lib.rt_last_error.restype = C.c_char_p
@@ -94,6 +114,7 @@ def b200() -> C.CDLL:
     lib.rt_render_device.argtypes = [vp, C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts), vp, vp]
     lib.rt_render_device_stats.argtypes = [vp, vp, C.POINTER(abi.rt_stats)]
     lib.rt_tonemap_device.argtypes = [vp, sz, i32, vp, vp]
+    lib.rt_tonemap.argtypes = [vp, sz, i32, vp]
     lib.rt_hit_batch.argtypes = [vp, u32, sz, vp, vp, f32, f32, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.rt_render_multi.argtypes = [C.POINTER(abi.rt_scene_desc), C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts),
                                     i32, vp, vp, C.POINTER(abi.rt_stats)]

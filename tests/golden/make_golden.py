@@ -129,8 +129,22 @@ def frames():
     print(f"-> {path.name} ({path.stat().st_size} B)")
 
 
+def tiffs():
+    """tests/golden/tiff.npz: files written by the reference's own write_tiff (src/tiff.c:15-49), RGB and gray."""
+    out = {}
+    for name, (w, h, c) in {"rgb_5x3": (5, 3, 3), "gray_4x2": (4, 2, 1), "rgb_300x2": (300, 2, 3)}.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            run(["tiff", 0, w, h, c, "out.tiff"], tmp)
+            out[name] = np.frombuffer(Path(tmp, "out.tiff").read_bytes(), dtype=np.uint8)
+    path = HERE / "tiff.npz"
+    np.savez_compressed(path, **out)
+    print(f"-> {path.name} ({path.stat().st_size} B)")
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "scenes"
+    if what in ("tiff", "all"):
+        tiffs()
     if what in ("scenes", "all"):
         main()
     if what in ("frames", "all"):

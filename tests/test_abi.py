@@ -177,3 +177,30 @@ def test_flattened_instances_are_counted_and_capped(rtc, scene_factory):
     d300 = instanced_scene(rtc, base, 300)
     info = rtc.inspect(d300)
     assert info["mega_supported"] == 0 and info["instances"] >= 255
+
+
+@pytest.mark.parametrize("name,shape", [("rgb_5x3", (5, 3, 3)), ("gray_4x2", (4, 2, 1)), ("rgb_300x2", (300, 2, 3))])
+def test_write_tiff_bytes_equal_the_reference_writer(rtc, tmp_path, name, shape):
+    """write_tiff (csrc/host/tiff_out.c) against files the reference's own writer produced
+    (/root/reference/src/tiff.c:15-49 through `ref_tool tiff`, tests/golden/make_golden.py tiff): the same bytes,
+    header, IFD, resolution rationals and strip, for RGB and for gray."""
+    import ctypes as C
+
+    from conftest import GOLDEN
+
+    want = np.load(GOLDEN / "tiff.npz")[name].tobytes()
+    w, h, c = shape
+    n = w * h * c
+    px = ((7 * np.arange(n, dtype=np.int64) + 3) % 251).astype(np.uint8)
+    host = rtc.lib.host()
+    libc = C.CDLL(None)
+    libc.fopen.restype = C.c_void_p
+    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
+    libc.fclose.argtypes = [C.c_void_p]
+    host.write_tiff.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    path = tmp_path / "out.tiff"
+    f = libc.fopen(str(path).encode(), b"wb")
+    assert f
+    assert host.write_tiff(f, w, h, c, px.ctypes.data_as(C.c_void_p)) == 0
+    libc.fclose(f)
+    assert path.read_bytes() == want

@@ -2,6 +2,7 @@
 reference's command line, TIFF output, and the multi-GPU entry points."""
 from __future__ import annotations
 
+import json
 import os
 import subprocess
 import tempfile
@@ -136,3 +137,114 @@ def test_dist_renderer_single_rank(rtc, scene_factory):
 def test_fp32_probe_reports_a_plausible_peak(rtc):
     tf = rtc.fp32_peak_tflops()
     assert 20.0 < tf < 120.0
+
+
+def _tiff_payload(path, width, height):
+    data = Path(path).read_bytes()
+    assert data[:4] == b"II*\x00"
+    assert int.from_bytes(data[8 + 2 + 8:8 + 2 + 10], "little") == width      # ImageWidth, first IFD entry
+    assert int.from_bytes(data[8 + 2 + 12 + 8:8 + 2 + 12 + 10], "little") == height
+    return np.frombuffer(data[-width * height * 3:], dtype=np.uint8).reshape(height, width, 3)
+
+
+def test_cli_named_options(rtc):
+    """rtc_main's options beyond the reference's positional arguments (src/main.c:280-292): --width / --spp (the
+    settings without the argv quirk), --depth, --aspect, --lights-prob, --out; the frame must be the one a Session
+    with the same settings renders, byte for byte."""
+    exe = rtc.lib.BUILD_DIR / "rtc_main"
+    with tempfile.TemporaryDirectory() as tmp:
+        env = dict(os.environ, RT_STATS="1")
+        proc = subprocess.run([str(exe), "6", "--width", "64", "--spp", "8", "--depth", "5", "--aspect", "2.0",
+                               "--lights-prob", "0.3", "--out", "cornell.tiff"], cwd=tmp, capture_output=True,
+                              text=True, env=env)
+        assert proc.returncode == 0, proc.stderr
+        assert not (Path(tmp) / "output.tiff").exists()
+        got = _tiff_payload(Path(tmp) / "cornell.tiff", 64, 32)
+        stats = json.loads([l for l in proc.stderr.splitlines() if l.startswith("{")][-1])
+    assert stats["samples"] == 64 * 32 * 8
+    sess = rtc.Session(6, width=64, spp=8, depth=5, aspect=2.0, lights_prob=0.3)
+    want, _, st = sess.camera_render(rtc.make_opts(kernel="mega", rng="sample"))
+    assert (sess.width, sess.height) == (64, 32)
+    assert np.array_equal(got, want)
+    assert stats["segments"] == st["segments"]
+    # depth is honoured: no path is longer than 5 segments
+    assert st["segments"] <= 5 * st["samples"]
+    # and the positional quirk is still the reference's: `6 64 8` (three arguments) sets the width, not the spp
+    with tempfile.TemporaryDirectory() as tmp:
+        proc = subprocess.run([str(exe), "6", "32", "8", "--depth", "2"], cwd=tmp, capture_output=True, text=True,
+                              env=dict(os.environ, RT_STATS="1"))
+        assert proc.returncode == 0, proc.stderr
+        stats = json.loads([l for l in proc.stderr.splitlines() if l.startswith("{")][-1])
+        assert stats["samples"] == 32 * 32 * 100
+
+
+def test_cli_progressive_passes_and_checkpoint_resume(rtc):
+    """--passes K renders the samples in K sample-range passes and --checkpoint saves the float sum after each; a
+    run killed after some passes and resumed must give the image of the uninterrupted run (the per-(pixel, sample)
+    streams make sample ranges additive)."""
+    exe = rtc.lib.BUILD_DIR / "rtc_main"
+    base = ["1", "--width", "96", "--spp", "24", "--depth", "20"]
+    with tempfile.TemporaryDirectory() as tmp:
+        one = subprocess.run([str(exe)] + base + ["--out", "one.tiff"], cwd=tmp, capture_output=True, text=True)
+        assert one.returncode == 0, one.stderr
+        prog = subprocess.run([str(exe)] + base + ["--passes", "4", "--checkpoint", "ck.bin", "--out", "prog.tiff"],
+                              cwd=tmp, capture_output=True, text=True)
+        assert prog.returncode == 0, prog.stderr
+        a, b = _tiff_payload(Path(tmp) / "one.tiff", 96, 54), _tiff_payload(Path(tmp) / "prog.tiff", 96, 54)
+        # same samples, summed in another order: at most the last bit of a sum, i.e. at most one 8-bit level
+        assert np.abs(a.astype(int) - b.astype(int)).max() <= 1
+        assert (a != b).mean() < 0.01
+        # a run that stops half way (--stop-after 2: two of the four passes of 6 samples), then is resumed
+        half = subprocess.run([str(exe)] + base + ["--passes", "4", "--stop-after", "2", "--checkpoint", "half.bin",
+                                                    "--out", "half.tiff"], cwd=tmp, capture_output=True, text=True)
+        assert half.returncode == 0, half.stderr
+        hdr = np.fromfile(Path(tmp) / "half.bin", dtype="<u4", count=5)
+        assert hdr[0] == 0x54435452 and tuple(hdr[1:4]) == (96, 54, 24) and hdr[4] == 12
+        res = subprocess.run([str(exe)] + base + ["--passes", "4", "--checkpoint", "half.bin", "--resume", "--out",
+                                                   "res.tiff"], cwd=tmp, capture_output=True, text=True)
+        assert res.returncode == 0 and "Resuming at sample 12 of 24" in res.stderr, res.stderr
+        c = _tiff_payload(Path(tmp) / "res.tiff", 96, 54)
+        assert np.array_equal(c, b)
+
+
+def test_camera_render_falls_back_when_the_rebuilt_structure_cannot_hold_the_scene(rtc):
+    """300 distinct Translate(RotateY(...)) chains exceed the 255 the throughput kernels can tag; the reference has no
+    such limit.  Camera_render must say so and render with the reference-order kernel instead of aborting."""
+    from conftest import ROOT
+
+    build = rtc.lib.BUILD_DIR
+    with tempfile.TemporaryDirectory() as tmp:
+        exe = Path(tmp) / "many_chains"
+        subprocess.run(["gcc", "-std=gnu11", "-O1", f"-I{ROOT / 'include'}", str(ROOT / "tests" / "c" / "many_chains.c"),
+                        "-o", str(exe), f"-L{build}", "-lrtc_host", "-lrtc_b200", f"-Wl,-rpath,{build}", "-lm"],
+                       check=True)
+        few = subprocess.run([str(exe), "40"], capture_output=True, text=True)
+        assert few.returncode == 0 and "RT_KERNEL=exact" not in few.stderr, few.stderr
+        many = subprocess.run([str(exe), "300"], capture_output=True, text=True)
+        assert many.returncode == 0, many.stderr
+        assert "RT_KERNEL=exact" in many.stderr and "255" in many.stderr
+        w, h, total = (int(v) for v in many.stdout.split())
+        assert (w, h) == (64, 32) and total > 64 * 32 * 3 * 20  # a lit frame, not a black one
+
+
+def test_camera_render_reuses_the_resident_scene(rtc):
+    """Camera_render goes through rt_scene_acquire / rt_scene_release: the second call on the same World must not
+    rebuild and upload (same pixels either way; the scene cache is keyed by the description's content)."""
+    import time
+
+    sess = rtc.Session(7, width=64, spp=2)
+    opts = rtc.make_opts(kernel="mega", rng="sample")
+    rgb_a, _, _ = sess.camera_render(opts)
+    t0 = time.perf_counter()
+    rgb_b, _, _ = sess.camera_render(opts)
+    warm = time.perf_counter() - t0
+    assert np.array_equal(rgb_a, rgb_b)
+    rtc.lib.b200().rt_shutdown()  # drops the idle cached scenes
+    t0 = time.perf_counter()
+    rgb_c, _, _ = sess.camera_render(opts)
+    cold = time.perf_counter() - t0
+    assert np.array_equal(rgb_a, rgb_c)
+    assert warm < cold  # the 2.5 MB scene with its 3 400 primitives is built and uploaded only when it is not resident
+    other = rtc.Session(7, width=64, spp=2, lights_prob=0.25)  # same World content, another camera: still a hit
+    rgb_d, _, _ = other.camera_render(opts)
+    assert rgb_d.shape == rgb_a.shape
