@@ -39,7 +39,11 @@ void rtc_camera_defaults(Camera *camera);
 int rtc_scene_build(int scene_id, World *world, Camera *camera);
 const char *rtc_scene_title(int scene_id);
 
-/* Image ingest */
+/* Image ingest (csrc/host/image_decode.c, image_io.c): PNG, baseline JPEG and binary PPM to RGB8, the bytes
+ * stbi_load(..., 3) gives the reference (/root/reference/src/texture.c:38-42).  rtc_load_image returns NULL with
+ * *exists = 0 when there is no such file, NULL with *exists = 1 and rtc_image_error() set when it cannot be decoded. */
+uint8_t *rtc_load_image(const char *filename, int *width, int *height, int *exists);
+const char *rtc_image_error(void);
 uint8_t *rtc_load_ppm(const char *filename, int *width, int *height);
 void rtc_synthetic_image(int width, int height, uint8_t *rgb);
 

@@ -209,7 +209,7 @@ RTC_DEV float s_div_z(float x, float y) {
  * (plus its slow path) is only paid by candidates near or inside the interval.  Most leaf candidates are not: a plane
  * hit behind the origin or beyond the best hit so far.  den must be a normal, non-zero number. */
 #ifndef RTC_DIV_PRETEST
-#define RTC_DIV_PRETEST 1
+#define RTC_DIV_PRETEST 0
 #endif
 RTC_DEV bool quotient_outside(float num, float den, float lo, float hi) {
 #if RTC_DIV_PRETEST
@@ -598,6 +598,20 @@ static __device__ __noinline__ float trace_early_call(const DScene &sc, const Ra
 template <bool EXACT>
 __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, float t_min, TraceHit &best, Rng &g) {
   float early_med_t = RTC_INF; /* closest medium hit the reference has accepted so far (even one that a later item beat) */
+  /* at most one medium whose acceptance is still open: it has drawn, it cannot win against the later item that holds
+   * the hit, and whether the reference accepted it (which needs its exact t_max, a restricted query) only matters if a
+   * medium further down the list asks for ITS exact t_max -- resolved then, usually never */
+  bool pend = false;
+  float pend_tm = 0.0f, pend_in = 0.0f, pend_out = 0.0f, pend_travel = 0.0f, pend_len = 0.0f;
+  uint32_t pend_node = 0u;
+  auto resolve = [&]() {
+    if (!pend)
+      return;
+    pend = false;
+    const float cap = fminf(pend_out, fminf(trace_early_call(sc, world, t_min, RTC_INF, pend_node), early_med_t));
+    if (!(pend_travel > s_mul(s_sub(cap, pend_in), pend_len)))
+      early_med_t = fminf(early_med_t, pend_tm);
+  };
   for (uint32_t m = 0; m < sc.n_media; m++) {
     const MMedium *med = &sc.media[m];
     Ray r = chain_apply_call(sc, med->op_begin, med->op_count, world);
@@ -630,7 +644,11 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
       /* `best` ends the interval before the entry.  An earlier item: no draw.  A later item: the reference still
        * draws, unless an EARLIER item (or an earlier medium's hit) ends the interval before the entry too */
       late = is_late(), late_known = true;
-      if (!late || fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
+      if (!late)
+        continue;
+      if (pend && pend_tm <= in_t)
+        resolve();
+      if (fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
         continue;
       sure = false;
     }
@@ -652,8 +670,16 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
     }
     if (!sure) {
       const bool beats = t_m < best.t || (t_m == best.t && REF_KIND(best.prim) == REF_SPHERES);
-      if (!beats && m + 1 >= sc.n_media)
-        continue; /* the later item keeps the hit either way and nobody is asked after this medium */
+      if (!beats) {
+        /* the later item keeps the hit whatever the reference decided: leave the decision open (see `pend`) */
+        if (m + 1 < sc.n_media) {
+          resolve();
+          pend = true, pend_tm = t_m, pend_in = in_t, pend_out = out.t, pend_travel = travel, pend_len = ray_len;
+          pend_node = med->node;
+        }
+        continue;
+      }
+      resolve();
       out_t = fminf(out.t, fminf(trace_early_call(sc, world, t_min, RTC_INF, med->node), early_med_t));
       if (travel > s_mul(s_sub(out_t, in_t), ray_len))
         continue;

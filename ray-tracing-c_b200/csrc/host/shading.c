@@ -128,13 +128,20 @@ Texture *Checker_new(float scale, Texture *even, Texture *odd) {
 /* ---- image texture ---- */
 
 void Image_init(Image *self, char *filename) {
+  /* texture.c:38-42: stbi_load(filename, &w, &h, NULL, 3) and an assert.  Here: PNG / baseline JPEG / binary PPM
+   * decoded by image_decode.c (same bytes as stb); a file that EXISTS but cannot be decoded stops the program like the
+   * reference's assert does; only when there is no such file does the synthetic procedural image stand in (the asset
+   * is not part of the reference repository; BASELINE.json: "synthetic procedural image if the asset is absent"). */
   self->texture.value = Image_value_tag;
-  self->buffer = rtc_load_ppm(filename, &self->width, &self->height);
+  int exists = 0;
+  self->buffer = rtc_load_image(filename, &self->width, &self->height, &exists);
+  if (self->buffer == NULL && exists) {
+    fprintf(stderr, "rtc_b200: cannot decode image '%s': %s\n", filename, rtc_image_error());
+    assert((self->buffer != NULL) && "Failed to load image");
+    abort(); /* (also under NDEBUG) */
+  }
   if (self->buffer == NULL) {
-    /* JPEG/PNG decoding is the reference's third-party stb_image and out of scope; BASELINE.json asks for a
-     * synthetic procedural image when the asset is absent. */
-    fprintf(stderr, "rtc_b200: image '%s' is absent or not a binary PPM; using the synthetic 1024x512 image\n",
-            filename);
+    fprintf(stderr, "rtc_b200: image '%s' is absent; using the synthetic 1024x512 image\n", filename);
     self->width = 1024;
     self->height = 512;
     self->buffer = my_malloc((size_t)self->width * self->height * 3);

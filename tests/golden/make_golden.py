@@ -141,10 +141,80 @@ def tiffs():
     print(f"-> {path.name} ({path.stat().st_size} B)")
 
 
+def _natural(w, h, seed):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    img = np.stack([128 + 100 * np.sin(x / 17.0 + y / 29.0), 128 + 90 * np.cos(x / 11.0 - y / 7.0), (x * 3 + y * 5) % 256], -1)
+    img = img + rng.normal(0, 12, img.shape)
+    img[h // 3:h // 3 + 5, w // 4:w // 4 + 9] = [255, 0, 40]
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def _adam7_png(rgb):
+    """An interlaced (Adam7) 8-bit RGB PNG, filter type 0 on every row (PIL cannot write interlaced files)."""
+    import struct
+    import zlib
+
+    h, w, _ = rgb.shape
+    raw = b""
+    for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+        sub = rgb[y0::dy, x0::dx]
+        if sub.shape[0] == 0 or sub.shape[1] == 0:
+            continue
+        for row in sub:
+            raw += b"\x00" + row.tobytes()
+
+    def chunk(kind, body):
+        return struct.pack(">I", len(body)) + kind + body + struct.pack(">I", zlib.crc32(kind + body))
+
+    return (b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 1)) +
+            chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
+def images():
+    """tests/golden/images/: small PNG and JPEG files (made with PIL) and, in stb.npz, what the reference's own
+    Image_init (src/texture.c:38-42: stbi_load(..., 3)) decodes from each -- through `ref_tool image`."""
+    from PIL import Image
+
+    out_dir = HERE / "images"
+    out_dir.mkdir(exist_ok=True)
+    for old in out_dir.iterdir():
+        old.unlink()
+    a, b = Image.fromarray(_natural(61, 37, 1)), Image.fromarray(_natural(48, 32, 2))
+    a.save(out_dir / "a_444_q90.jpg", quality=90, subsampling=0)
+    a.save(out_dir / "a_422_q75.jpg", quality=75, subsampling=1)
+    a.save(out_dir / "a_420_q50.jpg", quality=50, subsampling=2)
+    a.save(out_dir / "a_420_rst.jpg", quality=85, subsampling=2, restart_marker_blocks=2)
+    a.save(out_dir / "a_opt.jpg", quality=85, optimize=True)
+    a.convert("L").save(out_dir / "a_gray.jpg", quality=80)
+    Image.fromarray(_natural(1, 1, 3)).save(out_dir / "one_pixel.jpg", quality=90)
+    a.save(out_dir / "a_progressive.jpg", quality=80, progressive=True)  # decoded by stb, refused loudly here
+    b.save(out_dir / "b_rgb.png")
+    b.convert("RGBA").save(out_dir / "b_rgba.png")
+    b.convert("L").save(out_dir / "b_gray.png")
+    b.convert("LA").save(out_dir / "b_gray_alpha.png")
+    b.convert("P", palette=Image.ADAPTIVE, colors=17).save(out_dir / "b_palette.png")
+    b.convert("1").save(out_dir / "b_1bit.png")
+    Image.fromarray(_natural(48, 32, 2)[..., 0].astype(np.uint16) * 257 + 13).save(out_dir / "b_gray16.png")
+    (out_dir / "b_adam7.png").write_bytes(_adam7_png(_natural(21, 13, 4)))
+    decoded = {}
+    for path in sorted(out_dir.iterdir()):
+        with tempfile.TemporaryDirectory() as tmp:
+            run(["image", 0, path, "out.bin"], tmp)
+            raw = Path(tmp, "out.bin").read_bytes()
+        nl = raw.index(b"\n")
+        w, h = (int(v) for v in raw[:nl].split())
+        decoded[path.name] = np.frombuffer(raw[nl + 1:], np.uint8).reshape(h, w, 3)
+    np.savez_compressed(HERE / "images" / "stb.npz", **decoded)
+    print(f"-> images/ ({len(decoded)} files + stb.npz)")
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "scenes"
     if what in ("tiff", "all"):
         tiffs()
+    if what in ("images", "all"):
+        images()
     if what in ("scenes", "all"):
         main()
     if what in ("frames", "all"):
