@@ -648,7 +648,10 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
         continue;
       if (pend && pend_tm <= in_t)
         resolve();
-      if (fminf(trace_early_call(sc, world, t_min, in_t, med->node), early_med_t) <= in_t)
+      /* (the query's upper end is open for spheres, like Sphere_hit's: ask one ulp further and compare afterwards --
+       * the commonest occluder is the boundary's own surface, listed as an item before its medium, at exactly in_t) */
+      if (fminf(trace_early_call(sc, world, t_min, __uint_as_float(__float_as_uint(in_t) + 1u), med->node),
+                early_med_t) <= in_t)
         continue;
       sure = false;
     }
