@@ -628,6 +628,12 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
     mm.node = m.first;
     mm.neg_inv_density = n.f[0];
     mm.in_list = b.media_in_bvh.count(m.first) ? 0u : 1u;
+    mm.boundary_listed = 0;
+    const rt_node &top = d.nodes[d.objects_root];
+    if (mm.in_list && mm.op_count == 0 && d.nodes[n.a].kind == RT_NODE_SPHERE && top.kind == RT_NODE_LIST)
+      for (uint32_t k = 0; k < top.b && d.children[top.a + k] != m.first; k++)
+        if (d.children[top.a + k] == n.a)
+          mm.boundary_listed = 1;
     out.media.push_back(mm);
   }
   out.n_bnodes = (uint32_t)out.bnodes.size(), out.n_msph = (uint32_t)out.msph.size();

@@ -601,7 +601,13 @@ static int env_int(const char *name, int fallback) {
 static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class, int scene_feats) {
   int nv = env_int("RT_MEGA_NV", -99), minb = env_int("RT_MEGA_MINB", 0);
   if (nv == -99) {
-    nv = scene_class == MEGA_SCENE_SPHERES ? 0 : scene_class == MEGA_SCENE_MEDIA ? -2 : -1;
+    /* quads without media or textures (the Cornell box): the lean free-running kernel (9 318 Mseg/s) beats the lean
+     * lockstep one (8 583) -- what lockstep bought there was instruction-cache room the lean instantiation no longer
+     * needs */
+    const bool cornell_like = scene_class == MEGA_SCENE_QUADS &&
+                              (scene_feats & ~(FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS)) == 0 &&
+                              env_int("RT_MEGA_LEAN", 1) != 0;
+    nv = (scene_class == MEGA_SCENE_SPHERES || cornell_like) ? 0 : scene_class == MEGA_SCENE_MEDIA ? -2 : -1;
     if (minb == 0 && nv < 0)
       minb = scene_class == MEGA_SCENE_MEDIA ? 2 : 4;
   }

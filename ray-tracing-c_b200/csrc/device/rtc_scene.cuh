@@ -83,7 +83,10 @@ struct __align__(16) MMedium {
                                   evaluates it at its list position with the running t_max -- reproduced draw for draw
                                   (trace_media); 0: under a BVHNode, whose box test decides whether it is asked at all:
                                   evaluated after the surfaces (same distribution, other draw count) */
-  uint32_t pad;
+  uint32_t boundary_listed;    /* 1: the boundary is a plain sphere that is ALSO an item of world.objects before this
+                                  medium (Book 2 final lists the glass ball, then the fog inside it): a ray that enters
+                                  from outside meets that surface at exactly the entry distance, so an interval that
+                                  starts behind the closest hit is empty for the reference too -- no query needed */
 };
 
 struct DScene {

@@ -643,6 +643,8 @@ __device__ __noinline__ void trace_media(const DScene &sc, const Ray &world, flo
     if (in_t >= out_t) {
       /* `best` ends the interval before the entry.  An earlier item: no draw.  A later item: the reference still
        * draws, unless an EARLIER item (or an earlier medium's hit) ends the interval before the entry too */
+      if (med->boundary_listed)
+        continue; /* the boundary's own surface is an earlier item: it (or something nearer) ends the interval at in_t */
       late = is_late(), late_known = true;
       if (!late)
         continue;

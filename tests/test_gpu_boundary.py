@@ -118,6 +118,29 @@ def test_render_multi_shards_by_sample_range(rtc, scene_factory):
     assert (np.abs(rgb_2.astype(int) - rgb_1.astype(int)) <= 1).all()
 
 
+def test_camera_render_over_two_gpus_in_one_process(rtc):
+    """The literal drop-in at N > 1: `RT_GPUS=2 rtc_main ...` = Camera_render -> rt_render_multi -> one in-process
+    ncclReduce (communicator from ncclCommInitAll, kept between calls); with RT_MULTI_NCCL=0 the frames are gathered
+    over peer copies instead.  Both must give the one-GPU image (same per-(pixel, sample) streams; the float sums are
+    added in another order: at most one 8-bit level)."""
+    if rtc.lib.b200().rt_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    exe = rtc.lib.BUILD_DIR / "rtc_main"
+    images = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        for name, env in (("one", {"RT_GPUS": "1"}), ("nccl", {"RT_GPUS": "2"}),
+                          ("peer", {"RT_GPUS": "2", "RT_MULTI_NCCL": "0"})):
+            proc = subprocess.run([str(exe), "7", "--width", "96", "--spp", "16", "--out", f"{name}.tiff"], cwd=tmp,
+                                  capture_output=True, text=True, env=dict(os.environ, RT_STATS="1", **env))
+            assert proc.returncode == 0, proc.stderr
+            stats = json.loads([l for l in proc.stderr.splitlines() if l.startswith("{")][-1])
+            assert stats["n_gpus"] == int(env["RT_GPUS"]) and stats["samples"] == 96 * 96 * 16
+            images[name] = _tiff_payload(Path(tmp) / f"{name}.tiff", 96, 96)
+    for name in ("nccl", "peer"):
+        assert np.abs(images[name].astype(int) - images["one"].astype(int)).max() <= 1
+    assert np.array_equal(images["nccl"], images["peer"]) or (images["nccl"] != images["peer"]).mean() < 0.01
+
+
 def test_dist_renderer_single_rank(rtc, scene_factory):
     """The one-process-per-GPU driver with a world of one: rt_render_device on torch's stream + tonemap + D2H."""
     import importlib
