@@ -403,7 +403,10 @@ def b200_arm(args):
             image_check = image_diff(image_dist, whole)
             red = renderer.radiance.cpu().numpy()
             scale = np.maximum(np.abs(whole_rad), 1e-3 * args.spp)
-            image_check["radiance_max_rel_diff"] = float(np.max(np.abs(red - whole_rad) / scale))
+            rel = np.abs(red - whole_rad) / scale
+            finite = np.isfinite(rel)  # a NaN sample poisons its pixel's sum on both sides (as in the reference)
+            image_check["radiance_max_rel_diff"] = float(rel[finite].max()) if finite.any() else None
+            image_check["non_finite_values"] = [int((~np.isfinite(red)).sum()), int((~np.isfinite(whole_rad)).sum())]
             image_check["against"] = f"all {args.spp} spp rendered by rank 0's GPU alone (same per-(pixel,sample) streams)"
         else:
             image_check = image_diff(image_dist, rgb8_e2e)
