@@ -68,6 +68,7 @@ typedef struct PCG32 {
 
 void pcg32_seed(PCG32 *rng, uint64_t initstate, uint64_t initseq);
 uint32_t pcg32_u32(PCG32 *rng);
+void pcg32_advance(PCG32 *rng, uint64_t delta); /* extension: skip `delta` draws in O(log delta) */
 uint32_t pcg32_u32_between(PCG32 *rng, uint32_t lo, uint32_t hi); /* lo + u32 % (hi-lo), biased on purpose */
 float pcg32_f32(PCG32 *rng);                                      /* top 24 bits / 2^24, in [0,1) */
 float pcg32_f32_between(PCG32 *rng, float lo, float hi);

@@ -38,6 +38,23 @@ void pcg32_seed(PCG32 *rng, uint64_t initstate, uint64_t initseq) {
   (void)pcg32_u32(rng);
 }
 
+/* Jump `delta` draws ahead in O(log delta) (not in the reference, whose pcg32.c:11-17 only steps by one):
+ * the step state' = A * state + inc composed with itself delta times is state' = A^delta * state + inc * (A^delta - 1) /
+ * (A - 1), accumulated by repeated squaring of the affine map (Brown, "Random number generation with arbitrary
+ * strides").  After it the stream continues exactly as if pcg32_u32 had been called delta times. */
+void pcg32_advance(PCG32 *rng, uint64_t delta) {
+  uint64_t cur_mult = 6364136223846793005ULL, cur_plus = rng->inc, acc_mult = 1u, acc_plus = 0u;
+  while (delta > 0) {
+    if (delta & 1) {
+      acc_mult *= cur_mult;
+      acc_plus = acc_plus * cur_mult + cur_plus;
+    }
+    cur_plus = (cur_mult + 1) * cur_plus;
+    cur_mult *= cur_mult;
+    delta >>= 1;
+  }
+  rng->state = acc_mult * rng->state + acc_plus;
+}
 uint32_t pcg32_u32_between(PCG32 *rng, uint32_t lo, uint32_t hi) { return lo + pcg32_u32(rng) % (hi - lo); }
 float pcg32_f32(PCG32 *rng) { return (float)(pcg32_u32(rng) >> 8) / 16777216.0f; }
 float pcg32_f32_between(PCG32 *rng, float lo, float hi) { return lo + pcg32_f32(rng) * (hi - lo); }

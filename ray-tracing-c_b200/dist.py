@@ -44,7 +44,7 @@ class DistRenderer:
         rgb8, stats = r.render(kernel="mega")       # rgb8 is a numpy array on rank 0, None elsewhere
     """
 
-    def __init__(self, desc: abi.SceneDesc, camera: abi.rt_camera, device: int, group=None):
+    def __init__(self, desc: abi.SceneDesc, camera: abi.rt_camera, device: int, group=None, cached: bool = False):
         import torch
 
         self.torch = torch
@@ -52,7 +52,7 @@ class DistRenderer:
         torch.cuda.set_device(self.device)
         self.group = group
         self.camera = camera
-        self.scene = Scene(desc, device=device)
+        self.scene = Scene(desc, device=device, cached=cached)
         h, w = camera.img_height, camera.img_width
         self.radiance = torch.empty((h, w, 3), dtype=torch.float32, device=self.device)
         self.rgb8 = torch.empty((h, w, 3), dtype=torch.uint8, device=self.device)

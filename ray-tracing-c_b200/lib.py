@@ -28,7 +28,7 @@ B200_SYMBOLS = [
 ]
 HOST_SYMBOLS = [
     # the reference's API (include/rtc_api.h)
-    "Camera_init", "Camera_render", "World_init", "write_tiff", "my_malloc", "pcg32_seed", "pcg32_u32", "pcg32_f32",
+    "Camera_init", "Camera_render", "World_init", "write_tiff", "my_malloc", "pcg32_seed", "pcg32_u32", "pcg32_f32", "pcg32_advance",
     "HittableList_new", "HittableList_append", "Sphere_new", "Quad_new", "Box_new", "BVHNode_new", "Translate_new",
     "RotateY_new", "ConstantMedium_new", "Lambertian_new", "Metal_new", "Dielectric_new", "DiffuseLight_new",
     "Isotropic_new", "Solid_new", "Checker_new", "Image_new", "Perlin_new",

@@ -89,15 +89,25 @@ class Session:
 class Scene:
     """A flattened scene uploaded to one GPU (rt_scene_create)."""
 
-    def __init__(self, desc: abi.SceneDesc, device: int = -1):
+    def __init__(self, desc: abi.SceneDesc, device: int = -1, cached: bool = False):
+        """cached=True: rt_scene_acquire / rt_scene_release -- the uploaded scene comes from (and goes back to) the
+        library's cache keyed by the description's content, as Camera_render does; a second Scene of an equal
+        description skips the BVH build and the upload."""
         self._l = lib.b200()
         self.desc = desc
         self._p = C.c_void_p()
-        lib.check(self._l.rt_scene_create(C.byref(desc.c), device, C.byref(self._p)), "rt_scene_create")
+        self._cached = cached
+        if cached:
+            lib.check(self._l.rt_scene_acquire(C.byref(desc.c), device, C.byref(self._p)), "rt_scene_acquire")
+        else:
+            lib.check(self._l.rt_scene_create(C.byref(desc.c), device, C.byref(self._p)), "rt_scene_create")
 
     def close(self):
         if self._p:
-            self._l.rt_scene_destroy(self._p)
+            if self._cached:
+                self._l.rt_scene_release(self._p)
+            else:
+                self._l.rt_scene_destroy(self._p)
             self._p = C.c_void_p()
 
     def __del__(self):

@@ -101,6 +101,35 @@ def test_pcg32_known_answers(oracle):
     assert [int(v) for v in oracle.pcg32(42, 54, 6)] == want
 
 
+def test_pcg32_advance_equals_stepping(rtc, oracle):
+    """pcg32_advance (host extension, O(log n) jump-ahead over /root/reference/src/pcg32.c:11-17's single step): after
+    advancing by n the stream continues with the oracle's (n+1)-th value -- for small, large and power-of-two n."""
+    import ctypes as C
+
+    class PCG32(C.Structure):
+        _fields_ = [("state", C.c_uint64), ("inc", C.c_uint64)]
+
+    host = rtc.lib.host()
+    host.pcg32_seed.argtypes = [C.POINTER(PCG32), C.c_uint64, C.c_uint64]
+    host.pcg32_advance.argtypes = [C.POINTER(PCG32), C.c_uint64]
+    host.pcg32_u32.argtypes = [C.POINTER(PCG32)]
+    host.pcg32_u32.restype = C.c_uint32
+    want = [int(v) for v in oracle.pcg32(42, 54, 5000)]
+    for n in (0, 1, 2, 3, 6, 64, 1000, 4095, 4096):
+        g = PCG32()
+        host.pcg32_seed(C.byref(g), 42, 54)
+        host.pcg32_advance(C.byref(g), n)
+        assert [host.pcg32_u32(C.byref(g)) for _ in range(4)] == want[n:n + 4], n
+    # the affine map composes: advance(a) then advance(b) == advance(a + b), and 2^64 draws are the whole period
+    a, b = PCG32(), PCG32()
+    host.pcg32_seed(C.byref(a), 7, 9), host.pcg32_seed(C.byref(b), 7, 9)
+    host.pcg32_advance(C.byref(a), 123456789), host.pcg32_advance(C.byref(a), 2 ** 40 + 17)
+    host.pcg32_advance(C.byref(b), 123456789 + 2 ** 40 + 17)
+    assert a.state == b.state
+    host.pcg32_advance(C.byref(b), 2 ** 64 - 1), host.pcg32_u32(C.byref(b))
+    assert a.state == b.state
+
+
 def test_oracle_sample_mode_equals_pixel_mode_for_first_sample(rtc, oracle, scene_factory):
     """RT_RNG_SAMPLE seeds ((s<<32)|(17+j), 23+i): sample 0 is the reference's own stream."""
     sess, desc = scene_factory(0, 48, 1)

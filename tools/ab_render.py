@@ -23,13 +23,14 @@ def main():
     ap.add_argument("--frames", default="1:1200:200,6:600:200,7:1000:100", help="scene:width:spp[:aspect],...")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--kernel", default="mega")
+    ap.add_argument("--depth", type=int, default=50)
     ap.add_argument("--tag", default=os.environ.get("RTC_BUILD_DIR", "default"))
     args = ap.parse_args()
     for frame in args.frames.split(","):
         parts = frame.split(":")
         scene_id, width, spp = int(parts[0]), int(parts[1]), int(parts[2])
         aspect = float(parts[3]) if len(parts) > 3 else -1.0
-        sess = rtc.Session(scene_id, width=width, spp=spp, depth=50, aspect=aspect)
+        sess = rtc.Session(scene_id, width=width, spp=spp, depth=args.depth, aspect=aspect)
         scene = rtc.Scene(sess.flatten())
         opts = rtc.make_opts(kernel=args.kernel, rng="sample")
         scene.render(sess.camera, opts, want_radiance=False)
@@ -40,7 +41,7 @@ def main():
         scene.close()
         knobs = {k: v for k, v in os.environ.items() if k.startswith("RT_MEGA")}
         print(json.dumps({"tag": args.tag, "knobs": knobs, "scene": scene_id, "frame": [sess.width, sess.height],
-                          "spp": spp, "kernel_ms": best, "mseg_per_s": seg / best * 1e-3}), flush=True)
+                          "spp": spp, "depth": args.depth, "segments": seg, "kernel_ms": best, "mseg_per_s": seg / best * 1e-3}), flush=True)
 
 
 if __name__ == "__main__":
