@@ -74,6 +74,12 @@ struct rt_scene {
 
 namespace {
 
+inline float __uint_as_float_host(uint32_t u) {
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
 struct DeviceGuard {
   int previous = -1;
   explicit DeviceGuard(int device) {
@@ -368,6 +374,19 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   for (uint32_t k = 0; k < desc->n_materials; k++)
     if (desc->materials[k].tag == RT_MAT_ISOTROPIC)
       v.feats |= FEAT_MEDIA;
+  if (getenv("RT_CONST_CHAINS_OFF") == nullptr) {
+    for (uint32_t k = 0; k < 2 && k < built.n_insts; k++) {
+      const Instance &in = built.insts[k];
+      if (in.op_count < 1 || in.op_count > 2)
+        break; /* (instance k + 1 needs instance k to be there too: the leaf test compares tag <= n_const_chains) */
+      v.const_count[k] = in.op_count;
+      for (uint32_t j = 0; j < in.op_count; j++) {
+        const ChainOp &op = built.ops[in.op_begin + j];
+        v.const_op[k][j] = make_float4(op.f0, op.f1, op.f2, __uint_as_float_host(op.is_rotate));
+      }
+      v.n_const_chains = k + 1;
+    }
+  }
   if (desc->lights_root != RT_NONE && getenv("RT_ONE_LIGHT_OFF") == nullptr) {
     const rt_node &l = desc->nodes[desc->lights_root];
     if (l.kind == RT_NODE_LIST && l.b == 1 && desc->nodes[desc->children[l.a]].kind == RT_NODE_QUAD) {

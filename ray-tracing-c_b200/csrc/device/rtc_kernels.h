@@ -48,19 +48,26 @@ struct MegaPlan {
   int thr8;              /* node loop runs while >= thr8/8 of the busy lanes want it (walk_round_sync) */
   int resume8;           /* RESUME kernels: a trip's traversal ends once fewer than resume8/8 of its walkers remain */
   int cta8;              /* lockstep RESUME kernels: ... or once cta8/8 of the CTA's warps have finished theirs (0: off) */
-  int chunk;             /* samples per work item: the first n_big items of a pixel */
-  int n_big, small;      /* ... the remaining items take `small` samples each (guided self-scheduling: the items handed
-                            out last are short, so the lanes finish close together; see mega_plan) */
-  int n_chunks;          /* work items per pixel */
+  int chunk;             /* samples of a pixel's first (largest) work item */
+  int n_chunks;          /* work items per pixel (<= MEGA_MAX_CHUNKS) */
+  int begin[65];         /* first sample (relative to the job's sample_begin) of item c; begin[n_chunks] = sample count.
+                            Item sizes DECREASE (guided self-scheduling, see mega_plan): items are handed out chunk by
+                            chunk, and an item on an expensive pixel must not outlast everything handed out after it */
   size_t partial_bytes;  /* per-chunk partial sums when n_chunks > 1 */
 };
+#define MEGA_MAX_CHUNKS 64
 /* first sample (relative to the job's sample_begin) of a pixel's work item c; item c ends where item c + 1 begins */
-__host__ __device__ inline int plan_chunk_begin(const MegaPlan &p, int c) {
-#ifdef RTC_EXP_OLD_CHUNK
-  return c * p.chunk;
-#else
-  return c <= p.n_big ? c * p.chunk : p.n_big * p.chunk + (c - p.n_big) * p.small;
-#endif
+__host__ __device__ inline int plan_chunk_begin(const MegaPlan &p, int c) { return p.begin[c]; }
+/* equal items of `chunk` samples (the wavefront kernel, RT_MEGA_GUIDED=0, RT_MEGA_CHUNKS) */
+inline void plan_equal_chunks(MegaPlan *p, int sample_count, int n_chunks) {
+  if (n_chunks > MEGA_MAX_CHUNKS)
+    n_chunks = MEGA_MAX_CHUNKS;
+  if (n_chunks < 1)
+    n_chunks = 1;
+  p->chunk = (sample_count + n_chunks - 1) / n_chunks;
+  p->n_chunks = p->chunk > 0 ? (sample_count + p->chunk - 1) / p->chunk : 1;
+  for (int c = 0; c <= p->n_chunks; c++)
+    p->begin[c] = c * p->chunk < sample_count ? c * p->chunk : sample_count;
 }
 /* what the scene contains, as far as the choice of kernel variant goes (rtc_mega.cu: mega_variant) */
 enum { MEGA_SCENE_SPHERES = 0, MEGA_SCENE_QUADS = 1, MEGA_SCENE_MEDIA = 2 };

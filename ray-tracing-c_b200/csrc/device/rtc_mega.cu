@@ -23,6 +23,7 @@
 #define RTC_FAST_SHADING /* approximate div/sqrt in the shading code only; see rtc_math.cuh */
 #include "rtc_kernels.h"
 #include "rtc_trace.cuh"
+#include <cstdio>
 #include <cstdlib>
 
 #define MEGA_BLOCK 128
@@ -187,10 +188,15 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * suspended when few warps have work left). */
 template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS>
 __global__ void __launch_bounds__(BLOCK, MINB)
-    mega_render_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
+    mega_render_kernel(const __grid_constant__ DScene sc, const __grid_constant__ RenderJob job,
+                       const __grid_constant__ MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
   /* per-lane counts of one launch: a lane would need days to overflow 32 bits */
   unsigned n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+#ifdef RTC_TIMELINE /* development build: when does every CTA start, run out of items, and end? */
+  unsigned long long tl_in = 0, tl_dry = 0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_in));
+#endif
 
   /* per-lane path state */
   Rng rng;
@@ -239,6 +245,10 @@ __global__ void __launch_bounds__(BLOCK, MINB)
           have_item = true;
         } else {
           done = true;
+#ifdef RTC_TIMELINE
+          if (tl_dry == 0)
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_dry));
+#endif
         }
       }
       if (!done) {
@@ -331,6 +341,13 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   }
   /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
   flush_counters(job, n_segments, n_pdf, n_samples, n_nan);
+#ifdef RTC_TIMELINE
+  if (threadIdx.x == 0) {
+    unsigned long long tl_out;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_out));
+    printf("TL %u %llu %llu %llu %u\n", blockIdx.x, tl_in, tl_dry, tl_out, trip);
+  }
+#endif
 }
 
 /* ------------------------------------------------------------------ NV paths per lane, warp ray queue ----- */
@@ -369,7 +386,8 @@ RTC_DEV uint64_t rng_inc_of_column(int pi) { return ((23u + (uint64_t)pi) << 1u)
 
 template <int MINB, int NV>
 __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
-    mega_queue_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial) {
+    mega_queue_kernel(const __grid_constant__ DScene sc, const __grid_constant__ RenderJob job,
+                      const __grid_constant__ MegaPlan plan, float *partial) {
   const Frame f = frame_of(sc, job, plan);
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt_mask = (1u << lane) - 1u;
   WarpSlots<NV> S;
@@ -576,6 +594,7 @@ static const MegaVariant mega_variants[] = {
     /* nv = -2: lockstep CTAs whose trips do not wait for their longest rays (RESUME); nv = -3: the same, free-running */
     {-2, 2, mega_render_kernel<2, 512, true, true, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL},
     {-2, 4, mega_render_kernel<4, 256, true, true, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL},
+    {-2, 3, mega_render_kernel<2, 384, true, true, FEAT_ALL>, STACK_SMEM(384), 384, FEAT_ALL}, /* 80 registers */
     {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
     /* LEAN instantiations: the same kernels without the code of what a scene does not contain.  FEATS = 0: spheres
      * with solid-colour lambertian / metal / dielectric / emissive materials (scene 0, Book 1 final); quads + instances
@@ -670,31 +689,32 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
     n_chunks = (int)(want < 1 ? 1 : want);
     if (n_chunks > most)
       n_chunks = (int)(most < 1 ? 1 : most);
-    if (n_chunks > 64)
-      n_chunks = 64;
-    int env = env_int("RT_MEGA_CHUNKS", 0); /* tuning */
+    if (n_chunks > MEGA_MAX_CHUNKS)
+      n_chunks = MEGA_MAX_CHUNKS;
+    int env = env_int("RT_MEGA_CHUNKS", 0); /* tuning: that many EQUAL items */
     if (env > 0 && env <= sample_count)
       n_chunks = env;
   }
-  plan->chunk = (sample_count + n_chunks - 1) / n_chunks;
-  plan->n_chunks = plan->chunk > 0 ? (sample_count + plan->chunk - 1) / plan->chunk : 1;
-  plan->n_big = plan->n_chunks, plan->small = plan->chunk;
-  /* Guided self-scheduling: work items are handed out chunk by chunk (all pixels' item 0, then all pixels' item 1,
-   * ...), and the kernel ends when the LAST items end -- with equal items the lanes finish up to one item apart
-   * (measured on 8 GPUs, 125 spp per rank in 12 items of 11 samples: 0.98 ms of a 29.5 ms kernel).  So the last
-   * ~8 % of a pixel's samples go out in items a quarter as long; the chunks are still summed in order. */
-  if (plan->n_chunks > 1 && plan->chunk >= 8 && env_int("RT_MEGA_GUIDED", 1) != 0) {
-    const int small = plan->chunk / 4 > 2 ? plan->chunk / 4 : 2;
-    int tail = (sample_count * 2 + 24) / 25; /* 8 % of the samples ... */
-    tail = ((tail + small - 1) / small) * small; /* ... in whole small items */
-    if (tail < sample_count) {
-      const int n_big = (sample_count - tail + plan->chunk - 1) / plan->chunk;
-      const int rest = sample_count - n_big * plan->chunk;
-      if (n_big >= 1 && rest > 0) {
-        plan->n_big = n_big, plan->small = small;
-        plan->n_chunks = n_big + (rest + small - 1) / small;
-      }
+  plan_equal_chunks(plan, sample_count, n_chunks);
+  /* Guided self-scheduling.  Work items are handed out chunk by chunk (all pixels' item 0, then all pixels' item 1,
+   * ...) and the kernel ends when the LAST item ends.  Items cost very differently: a pixel on a glass sphere runs
+   * depth-50 paths, ~18x the average sample.  With equal items one such item handed out near the end outlasts
+   * everything else: timestamps (tools/timeline.py, Book 1 at 125 spp per GPU) show the queue empty at 25.1 ms, the
+   * median CTA done at 25.2 ms and the last one at 27.3 ms.  So an item takes a QUARTER of the samples its pixel has
+   * left (at least one): whatever an expensive pixel's item costs, three times as much work is still to be handed out
+   * behind it.  The chunks are still summed in order (mega_sum_chunks_kernel): images stay deterministic. */
+  if (n_chunks > 1 && env_int("RT_MEGA_GUIDED", 1) != 0 && env_int("RT_MEGA_CHUNKS", 0) <= 0) {
+    int c = 0, at = 0;
+    while (at < sample_count && c < MEGA_MAX_CHUNKS - 1) {
+      plan->begin[c++] = at;
+      const int left = sample_count - at;
+      at += left / 4 > 1 ? left / 4 : 1;
     }
+    if (at < sample_count) /* (more than 64 items are never needed below ~1e8 samples; the last one takes the rest) */
+      plan->begin[c++] = at;
+    plan->begin[c] = sample_count;
+    plan->n_chunks = c;
+    plan->chunk = plan->begin[1] - plan->begin[0];
   }
   plan->partial_bytes = plan->n_chunks > 1 ? (size_t)plan->n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
   if (mega_variant(cam, plan->n_chunks, scene_class, scene_feats) != var) { /* capacity check failed: the register kernel */

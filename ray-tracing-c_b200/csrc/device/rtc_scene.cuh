@@ -114,6 +114,12 @@ struct DScene {
   /* world.lights is a list of exactly ONE quad (Cornell box, Book 2 final): the quad itself, here in the kernel's
    * parameter space (constant bank, warp-uniform reads), so HittableList_pdf / _rand need no walk over the graph */
   uint32_t feats;          /* FEAT_* mask of what the scene contains */
+  /* the transform chains of instances 1 and 2, when each is at most two steps (Translate(RotateY(x)): the Cornell
+   * box's two blocks, Book 2 final's sphere cluster), in the kernel's parameter space: a tagged leaf then moves the ray
+   * without the two dependent loads (instance record, then its steps) it otherwise starts with */
+  uint32_t n_const_chains; /* 0, 1 or 2 */
+  uint32_t const_count[2];
+  float4 const_op[2][2];   /* ChainOp bits: f0 f1 f2 is_rotate */
   uint32_t one_quad_light; /* 1: `light` is valid */
   rt_quad light;
 };

@@ -40,6 +40,9 @@
 #ifndef RTC_MEDIA_INLIST
 #define RTC_MEDIA_INLIST 1 /* 0: media clipped against the closest surface whatever its list position (round 1) */
 #endif
+#ifndef RTC_CONST_CHAINS
+#define RTC_CONST_CHAINS 1
+#endif
 #ifndef RTC_POSTPONE
 #define RTC_POSTPONE 1 /* 1: kernels of <= 256 threads park the first leaf of a round and keep descending; 2: all; 0: none */
 #endif
@@ -65,16 +68,18 @@ struct Ray {
 /* world (or enclosing-frame) ray -> object frame, op by op like Translate_hit / RotateY_hit (hittable.c:325-367) */
 /* (out of line: entering an instance is rare next to a node visit, and the kernels are instruction-cache bound on
  * the scenes that have instances -- see DESIGN.md) */
-RTC_CHAIN_ATTR Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
-  for (uint32_t k = 0; k < op_count; k++) {
-    const float4 op = __ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k]));
-    if (__float_as_uint(op.w) == 0u) {
-      r.o = sv_sub(r.o, v3(op.x, op.y, op.z));
-    } else {
-      r.o = sv_rot_y(r.o, op.y, op.x);
-      r.d = sv_rot_y(r.d, op.y, op.x);
-    }
+RTC_DEV Ray chain_step(float4 op, Ray r) {
+  if (__float_as_uint(op.w) == 0u) {
+    r.o = sv_sub(r.o, v3(op.x, op.y, op.z));
+  } else {
+    r.o = sv_rot_y(r.o, op.y, op.x);
+    r.d = sv_rot_y(r.d, op.y, op.x);
   }
+  return r;
+}
+RTC_CHAIN_ATTR Ray chain_apply(const DScene &sc, uint32_t op_begin, uint32_t op_count, Ray r) {
+  for (uint32_t k = 0; k < op_count; k++)
+    r = chain_step(__ldg(reinterpret_cast<const float4 *>(&sc.ops[op_begin + k])), r);
   return r;
 }
 /* object frame -> world for a hit point and its normal, innermost op first */
@@ -420,8 +425,20 @@ template <int SK, int FEATS = FEAT_ALL> struct WalkerT {
     Ray r = outer();
     float a = d_len2;
     if ((FEATS & FEAT_INSTANCES) && tag != 0u) {
-      const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[tag - 1u]));
-      r = chain_apply(sc, inst.x, inst.y, r);
+      if (RTC_CONST_CHAINS && tag <= sc.n_const_chains) {
+        /* instance 1 or 2, at most two steps: from the parameter bank (selected, not indexed: an indexed access
+         * would make the compiler copy the parameters to local memory) */
+        const bool first = tag == 1u;
+        const float4 op0 = first ? sc.const_op[0][0] : sc.const_op[1][0];
+        const float4 op1 = first ? sc.const_op[0][1] : sc.const_op[1][1];
+        const uint32_t n_ops = first ? sc.const_count[0] : sc.const_count[1];
+        r = chain_step(op0, r);
+        if (n_ops > 1u)
+          r = chain_step(op1, r);
+      } else {
+        const uint2 inst = __ldg(reinterpret_cast<const uint2 *>(&sc.insts[tag - 1u]));
+        r = chain_apply(sc, inst.x, inst.y, r);
+      }
       a = sv_len2(r.d);
     }
     /* a Box leaf is its six quads in list order, each against the running best (closed interval: a later face wins

@@ -149,7 +149,7 @@ RTC_DEV void wave_count(unsigned long long *counter, unsigned mine) {
 }
 
 __global__ void __launch_bounds__(WAVE_BLOCK)
-    wave_fill_kernel(const RenderJob job, const MegaPlan plan, float *partial, WavePool pool) {
+    wave_fill_kernel(const RenderJob job, const __grid_constant__ MegaPlan plan, float *partial, WavePool pool) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned started = 0;
   if (slot < pool.slots) {
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(WAVE_BLOCK)
 /* ------------------------------------------------------------------ shade -------------------------------- */
 
 __global__ void __launch_bounds__(WAVE_BLOCK)
-    wave_shade_kernel(const DScene sc, const RenderJob job, const MegaPlan plan, float *partial, WavePool pool,
+    wave_shade_kernel(const DScene sc, const RenderJob job, const __grid_constant__ MegaPlan plan, float *partial, WavePool pool,
                       int parity) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0) { /* the other parity's counters are read by nobody now: reset them for the next extend */
@@ -346,9 +346,7 @@ cudaError_t wave_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
       n_chunks = atoi(chunk_env);
   }
   plan->mega.blocks = 0, plan->mega.threads = 0, plan->mega.minb = 0, plan->mega.nv = 0;
-  plan->mega.chunk = (sample_count + n_chunks - 1) / n_chunks;
-  plan->mega.n_chunks = (sample_count + plan->mega.chunk - 1) / plan->mega.chunk;
-  plan->mega.n_big = plan->mega.n_chunks, plan->mega.small = plan->mega.chunk; /* equal items */
+  plan_equal_chunks(&plan->mega, sample_count, n_chunks);
   plan->mega.partial_bytes =
       plan->mega.n_chunks > 1 ? (size_t)plan->mega.n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
   /* pool: many full waves of every SM per launch (the two launches of an iteration cost a few microseconds of
