@@ -266,6 +266,21 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, flo
  * (a cudaStream_t, NULL = default stream).  For one-process-per-GPU drivers that reduce with NCCL afterwards. */
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, float *radiance_sum_dev,
                      void *cuda_stream);
+/* rt_render_device WITHOUT ANY ALLOCATION, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  This entry point has no counterpart in the reference.
+ * Same render (RT_KERNEL_MEGA only), same arguments, asynchronous on
+ * `cuda_stream`; the kernel's scratch -- render counters and per-chunk partial sums -- lives in ONE file-scope device
+ * array of RT_NOALLOC_SCRATCH_BYTES (32 MiB, held by every GPU that loads the library until the process exits)
+ * instead of pool memory, and the call performs no cudaMalloc / cudaFree / cudaMallocAsync of any kind.
+ * Limit: frames of at most RT_NOALLOC_MAX_PIXELS pixels (two partial-sum frames of 12 bytes per pixel must fit);
+ * larger frames and the other kernels are refused with RT_ERR_INVALID / RT_ERR_UNSUPPORTED and a message.  Fewer
+ * partial frames than rt_render_device would use means a coarser work-item split (the sums differ in the last bits).
+ * All calls SHARE the array: calls that overlap on the GPU (two streams, two threads, two scenes on one device) race;
+ * serialise them.  The counters are in the array too, so rt_render_device_stats does not see this call. */
+#define RT_NOALLOC_SCRATCH_BYTES (32u << 20)
+#define RT_NOALLOC_MAX_PIXELS (RT_NOALLOC_SCRATCH_BYTES / (2u * 3u * 4u))
+int rt_render_device_noalloc(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, float *radiance_sum_dev,
+                             void *cuda_stream);
 /* Waits for `cuda_stream` and returns the counters of the last rt_render_device on this scene. */
 int rt_render_device_stats(rt_scene *scene, void *cuda_stream, rt_stats *stats);
 

@@ -984,6 +984,93 @@ extern "C" int rt_render_multi(const rt_scene_desc *desc, const rt_camera *camer
 #undef MULTI_TRY
 }
 
+/* ------------------------------------------------------------------ render without allocation ------------ */
+
+/* Scratch of rt_render_device_noalloc: the render counters (first 256 bytes) and the per-chunk partial sums of the
+ * megakernel, in a file-scope array instead of pool memory.  Every GPU that loads the library holds these 32 MiB
+ * until the process exits.  NOTE: in host code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a
+ * device address -- only cudaGetSymbolAddress gives the pointer a kernel can use (noalloc_scratch below). */
+#define NOALLOC_HEAD_BYTES 256u
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_HEAD_BYTES + RT_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_noalloc_mutex;
+void *g_noalloc_ptr[64] = {nullptr};
+
+/* device address of the array on `device` (which must be current): looked up once per device */
+int noalloc_scratch(int device, unsigned char **out) {
+  if (device < 0 || device >= 64)
+    return fail(RT_ERR_INVALID, "rt_render_device_noalloc: device %d out of range", device);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device]) {
+    void *ptr = nullptr;
+    cudaError_t err = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (err != cudaSuccess || !ptr)
+      return fail(RT_ERR_CUDA, "rt_render_device_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(err));
+    g_noalloc_ptr[device] = ptr;
+  }
+  *out = static_cast<unsigned char *>(g_noalloc_ptr[device]);
+  return RT_OK;
+}
+} // namespace
+
+extern "C" int rt_render_device_noalloc(rt_scene *scene, const rt_camera *camera, const rt_opts *opts,
+                                        float *radiance_sum_dev, void *cuda_stream) {
+  if (!scene || !camera || !opts || !radiance_sum_dev)
+    return fail(RT_ERR_INVALID, "rt_render_device_noalloc: NULL argument");
+  if (opts->kernel != RT_KERNEL_MEGA)
+    return fail(RT_ERR_UNSUPPORTED, "rt_render_device_noalloc: only RT_KERNEL_MEGA renders without allocating "
+                                    "(the exact and wavefront kernels need scratch far beyond the static array)");
+  if (!scene->mega_ok)
+    return fail(RT_ERR_UNSUPPORTED, "rt_render_device_noalloc: %s", scene->mega_why.c_str());
+  int begin = 0, count = 0;
+  int rc = resolve_range(camera, opts, &begin, &count);
+  if (rc != RT_OK)
+    return rc;
+  /* the maximum: two partial-sum frames (12 bytes per pixel each) must fit the array */
+  const unsigned long long pixels = (unsigned long long)camera->img_width * (unsigned long long)camera->img_height;
+  if (pixels > RT_NOALLOC_MAX_PIXELS)
+    return fail(RT_ERR_INVALID, "rt_render_device_noalloc: frame %dx%d = %llu pixels exceeds the maximum of %llu pixels "
+                                "(static scratch of %u bytes); use rt_render_device",
+                camera->img_width, camera->img_height, pixels, (unsigned long long)RT_NOALLOC_MAX_PIXELS,
+                (unsigned)RT_NOALLOC_SCRATCH_BYTES);
+  DeviceGuard guard(scene->device);
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  unsigned char *scratch = nullptr;
+  rc = noalloc_scratch(scene->device, &scratch);
+  if (rc != RT_OK)
+    return rc;
+
+  MegaPlan plan;
+  const int scene_class = scene->view.n_media           ? MEGA_SCENE_MEDIA
+                          : scene->built_info.n_mquads ? MEGA_SCENE_QUADS
+                                                       : MEGA_SCENE_SPHERES;
+  CUDA_TRY(mega_plan(*camera, count, opts->rng_mode, scene->device, scene_class, (int)scene->view.feats, &plan));
+  /* as many work items per pixel as partial-sum frames fit: the trailing items are merged into the last one */
+  const size_t frame_bytes = (size_t)pixels * 3 * sizeof(float);
+  const int cap = (int)(RT_NOALLOC_SCRATCH_BYTES / frame_bytes);
+  if (plan.n_chunks > cap) {
+    plan.n_chunks = cap; /* >= 2 by the size check above */
+    plan.begin[cap] = count;
+  }
+  plan.partial_bytes = plan.n_chunks > 1 ? (size_t)plan.n_chunks * frame_bytes : 0;
+
+  RenderJob job;
+  memset(&job, 0, sizeof(job));
+  job.cam = *camera;
+  job.sample_begin = begin, job.sample_count = count;
+  job.rng_mode = opts->rng_mode, job.flags = opts->flags;
+  job.radiance = radiance_sum_dev;
+  job.counters = reinterpret_cast<RenderCounters *>(scratch);
+  /* the array keeps the last call's contents: the counters (work-item cursor!) must start at zero; every partial
+   * sum a launch reads was written by that launch */
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, NOALLOC_HEAD_BYTES, stream));
+  int launches = 0;
+  CUDA_TRY(mega_render(scene->view, job, plan, reinterpret_cast<float *>(scratch + NOALLOC_HEAD_BYTES), stream,
+                       &launches));
+  return RT_OK;
+}
+
 /* ------------------------------------------------------------------ FP32 roofline probe ------------------ */
 
 __global__ void fp32_peak_kernel(float *out, int iters) {

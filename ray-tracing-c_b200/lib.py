@@ -23,7 +23,7 @@ REPO_ROOT = PKG_DIR.parent
 B200_SYMBOLS = [
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_scene_inspect", "rt_scene_create", "rt_scene_destroy",
     "rt_scene_acquire", "rt_scene_release", "rt_shutdown", "rt_render",
-    "rt_render_device", "rt_render_device_stats", "rt_tonemap_device", "rt_tonemap", "rt_hit_batch", "rt_render_multi",
+    "rt_render_device", "rt_render_device_noalloc", "rt_render_device_stats", "rt_tonemap_device", "rt_tonemap", "rt_hit_batch", "rt_render_multi",
     "rt_fp32_peak",
 ]
 HOST_SYMBOLS = [
@@ -112,6 +112,7 @@ def b200() -> C.CDLL:
     lib.rt_scene_destroy.restype = None
     lib.rt_render.argtypes = [vp, C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts), vp, vp, C.POINTER(abi.rt_stats)]
     lib.rt_render_device.argtypes = [vp, C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts), vp, vp]
+    lib.rt_render_device_noalloc.argtypes = [vp, C.POINTER(abi.rt_camera), C.POINTER(abi.rt_opts), vp, vp]
     lib.rt_render_device_stats.argtypes = [vp, vp, C.POINTER(abi.rt_stats)]
     lib.rt_tonemap_device.argtypes = [vp, sz, i32, vp, vp]
     lib.rt_tonemap.argtypes = [vp, sz, i32, vp]

@@ -132,6 +132,12 @@ class Scene:
         rc = self._l.rt_render_device(self._p, C.byref(camera), C.byref(opts), radiance_ptr, stream_ptr or None)
         lib.check(rc, "rt_render_device")
 
+    def render_device_noalloc(self, camera: abi.rt_camera, opts: abi.rt_opts, radiance_ptr: int, stream_ptr: int = 0):
+        """rt_render_device_noalloc: the same render with its scratch in the library's static device array -- no
+        allocation in the call; frames up to RT_NOALLOC_MAX_PIXELS; calls that overlap on the GPU race."""
+        rc = self._l.rt_render_device_noalloc(self._p, C.byref(camera), C.byref(opts), radiance_ptr, stream_ptr or None)
+        lib.check(rc, "rt_render_device_noalloc")
+
     def device_stats(self, stream_ptr: int = 0) -> dict:
         stats = abi.rt_stats()
         lib.check(self._l.rt_render_device_stats(self._p, stream_ptr or None, C.byref(stats)), "rt_render_device_stats")
