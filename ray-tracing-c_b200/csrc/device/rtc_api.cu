@@ -354,6 +354,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   UP(images, desc->images, desc->n_images);
   UP(texels, desc->texels, desc->n_texel_bytes);
   UP(bnodes, built.bnodes.data(), built.bnodes.size());
+  UP(wnodes, built.wnodes.data(), built.wnodes.size());
   UP(msph, built.msph.data(), built.msph.size());
   UP(msph_meta, built.msph_meta.data(), built.msph_meta.size());
   UP(mquads, built.mquads.data(), built.mquads.size());
@@ -364,6 +365,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   v.objects_root = desc->objects_root;
   v.lights_root = desc->lights_root;
   v.world_root = built.world_root;
+  v.wide_root = (built.wide_root != REF_EMPTY && built.wide_max_stack + 2 <= TRACE_STACK) ? built.wide_root : REF_EMPTY;
   v.n_media = (uint32_t)built.media.size();
   v.n_perlins = desc->n_perlins;
   v.feats = (built.n_mquads ? FEAT_QUADS : 0) | (built.n_insts ? FEAT_INSTANCES : 0) |
@@ -405,7 +407,7 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
     rt_scene_destroy(s);
     return rc;
   }
-  built.bnodes.clear(), built.msph.clear(), built.msph_meta.clear(), built.mquads.clear();
+  built.bnodes.clear(), built.wnodes.clear(), built.msph.clear(), built.msph_meta.clear(), built.mquads.clear();
   s->built_info = built;
   *out = s;
   return RT_OK;
@@ -544,7 +546,7 @@ static int enqueue_render(rt_scene *s, const rt_camera *cam, const rt_opts *opts
     const int scene_class = s->view.n_media           ? MEGA_SCENE_MEDIA
                             : s->built_info.n_mquads ? MEGA_SCENE_QUADS
                                                      : MEGA_SCENE_SPHERES;
-    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, scene_class, (int)s->view.feats, &plan));
+    CUDA_TRY(mega_plan(*cam, count, opts->rng_mode, s->device, scene_class, (int)s->view.feats | (s->view.wide_root != REF_EMPTY ? MEGA_FEATS_WIDE_TREE : 0), &plan));
     rc = ensure(&s->scratch, &s->scratch_bytes, plan.partial_bytes);
     if (rc != RT_OK)
       return rc;
@@ -1045,7 +1047,7 @@ extern "C" int rt_render_device_noalloc(rt_scene *scene, const rt_camera *camera
   const int scene_class = scene->view.n_media           ? MEGA_SCENE_MEDIA
                           : scene->built_info.n_mquads ? MEGA_SCENE_QUADS
                                                        : MEGA_SCENE_SPHERES;
-  CUDA_TRY(mega_plan(*camera, count, opts->rng_mode, scene->device, scene_class, (int)scene->view.feats, &plan));
+  CUDA_TRY(mega_plan(*camera, count, opts->rng_mode, scene->device, scene_class, (int)scene->view.feats | (scene->view.wide_root != REF_EMPTY ? MEGA_FEATS_WIDE_TREE : 0), &plan));
   /* as many work items per pixel as partial-sum frames fit: the trailing items are merged into the last one */
   const size_t frame_bytes = (size_t)pixels * 3 * sizeof(float);
   const int cap = (int)(RT_NOALLOC_SCRATCH_BYTES / frame_bytes);

@@ -244,6 +244,7 @@ struct Builder {
   const rt_scene_desc &d;
   BuiltScene &out;
   const bool kBoxLeaves = box_leaves_enabled();
+  std::vector<Box> child_boxes; /* 2 per binary node: the exact (lo, hi) boxes the (centre, half) forms were made from */
   Builder(const rt_scene_desc &desc, BuiltScene &o) : d(desc), out(o) {}
 
   static Box node_box(const rt_node &n) {
@@ -580,7 +581,64 @@ struct Builder {
 #endif
     node.child0 = c0, node.child1 = c1, node.pad0 = 0, node.pad1 = 0;
     out.bnodes[self] = node;
+    if (child_boxes.size() < 2 * out.bnodes.size())
+      child_boxes.resize(2 * out.bnodes.size());
+    child_boxes[2 * self] = b0, child_boxes[2 * self + 1] = b1;
     depth = 1 + std::max(d0, d1);
+    return MAKE_REF(REF_INNER, 0, self);
+  }
+
+  /* The binary subtree under `ref` as a 4-wide tree: a node's two children are replaced, largest surface first, by
+   * their own children until there are four (or only leaves are left).  Returns the wide reference; `stack_need` =
+   * the most entries a walk below it can have pushed at once (every visit pushes at most children - 1). */
+  uint32_t wide_collapse(uint32_t ref, int &stack_need) {
+    stack_need = 0;
+    if (ref == REF_EMPTY || REF_KIND(ref) != REF_INNER)
+      return ref;
+    struct Kid {
+      uint32_t ref;
+      Box box;
+    };
+    std::vector<Kid> kids;
+    const BNode &root = out.bnodes[ref];
+    kids.push_back(Kid{root.child0, child_boxes[2 * ref]});
+    kids.push_back(Kid{root.child1, child_boxes[2 * ref + 1]});
+    while (kids.size() < 4) {
+      int pick = -1;
+      for (size_t k = 0; k < kids.size(); k++)
+        if (REF_KIND(kids[k].ref) == REF_INNER && (pick < 0 || kids[k].box.area() > kids[(size_t)pick].box.area()))
+          pick = (int)k;
+      if (pick < 0)
+        break;
+      const uint32_t inner = kids[(size_t)pick].ref;
+      const BNode &n = out.bnodes[inner];
+      kids[(size_t)pick] = Kid{n.child0, child_boxes[2 * inner]};
+      kids.push_back(Kid{n.child1, child_boxes[2 * inner + 1]});
+    }
+    const uint32_t self = (uint32_t)out.wnodes.size();
+    out.wnodes.push_back(WNode());
+    WNode w;
+    memset(&w, 0, sizeof(w));
+    float c[3][4], h[3][4];
+    int deepest = 0;
+    for (size_t k = 0; k < 4; k++) {
+      if (k < kids.size()) {
+        int below = 0;
+        w.child[k] = wide_collapse(kids[k].ref, below);
+        deepest = std::max(deepest, below);
+        for (int a = 0; a < 3; a++)
+          centre_half(kids[k].box.lo[a], kids[k].box.hi[a], c[a][k], h[a][k]);
+      } else {
+        w.child[k] = REF_EMPTY;
+        for (int a = 0; a < 3; a++)
+          c[a][k] = 0.0f, h[a][k] = 0.0f;
+      }
+    }
+    w.cx = make_float4(c[0][0], c[0][1], c[0][2], c[0][3]), w.hx = make_float4(h[0][0], h[0][1], h[0][2], h[0][3]);
+    w.cy = make_float4(c[1][0], c[1][1], c[1][2], c[1][3]), w.hy = make_float4(h[1][0], h[1][1], h[1][2], h[1][3]);
+    w.cz = make_float4(c[2][0], c[2][1], c[2][2], c[2][3]), w.hz = make_float4(h[2][0], h[2][1], h[2][2], h[2][3]);
+    out.wnodes[self] = w;
+    stack_need = (int)kids.size() - 1 + deepest;
     return MAKE_REF(REF_INNER, 0, self);
   }
 
@@ -610,6 +668,11 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
   int depth = 0;
   out.world_root = b.build_group(d.objects_root, false, media, depth);
   out.max_stack = depth;
+  if (env_float("RT_BVH_WIDE", 0.0f) != 0.0f && RTC_NODE_CH) { /* the world group again, four children per node */
+    int need = 0;
+    out.wide_root = b.wide_collapse(out.world_root, need);
+    out.wide_max_stack = need;
+  }
   for (auto &m : media) {
     const rt_node &n = d.nodes[m.first];
     MMedium mm;
@@ -642,6 +705,8 @@ void rtc_build_scene(const rt_scene_desc &d, BuiltScene &out) {
   /* keep every array non-empty so device pointers are never NULL */
   if (out.bnodes.empty())
     out.bnodes.push_back(BNode());
+  if (out.wnodes.empty())
+    out.wnodes.push_back(WNode());
   if (out.msph.empty()) {
     out.msph.push_back(MSphere{0, 0, 0, 0});
     out.msph_meta.push_back(MPrimMeta{0, 0});

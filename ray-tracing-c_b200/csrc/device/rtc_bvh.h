@@ -18,6 +18,9 @@
 
 struct BuiltScene {
   std::vector<BNode> bnodes;
+  std::vector<WNode> wnodes;         /* world group only, when requested (RT_BVH_WIDE=1) */
+  uint32_t wide_root = REF_EMPTY;
+  int wide_max_stack = 0;
   std::vector<MSphere> msph;
   std::vector<MPrimMeta> msph_meta;
   std::vector<MQuad> mquads;

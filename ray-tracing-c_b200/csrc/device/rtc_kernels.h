@@ -71,6 +71,7 @@ inline void plan_equal_chunks(MegaPlan *p, int sample_count, int n_chunks) {
 }
 /* what the scene contains, as far as the choice of kernel variant goes (rtc_mega.cu: mega_variant) */
 enum { MEGA_SCENE_SPHERES = 0, MEGA_SCENE_QUADS = 1, MEGA_SCENE_MEDIA = 2 };
+#define MEGA_FEATS_WIDE_TREE (1 << 30) /* or'ed into scene_feats: walk the scene's 4-wide tree (DScene.wnodes) */
 /* scene_feats: FEAT_* mask of the scene (rtc_scene.cuh): a kernel without the code of absent features is preferred */
 cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode, int device, int scene_class,
                       int scene_feats, MegaPlan *plan);

@@ -186,7 +186,7 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * issues of a warp there): once plan.cta8/8 of the CTA's warps have finished the trip's traversal, the others suspend
  * theirs too (after at least one round, so every trip makes progress; warps without work do not count, so nobody is
  * suspended when few warps have work left). */
-template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS>
+template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS, int NW = 2>
 __global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const __grid_constant__ DScene sc, const __grid_constant__ RenderJob job,
                        const __grid_constant__ MegaPlan plan, float *partial) {
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   bool have_item = false, alive = false;
   /* the traversal state outlives a trip only in the RESUME kernels */
   uint32_t stack[TRACE_STACK - RTC_SMEM_STACK];
-  WalkerT<RTC_SMEM_STACK, FEATS> wk;
+  WalkerT<RTC_SMEM_STACK, FEATS, NW> wk; /* NW = 4: the world group's 4-wide tree (sc.wnodes) */
   wk.stack = stack, wk.cur = REF_EMPTY, wk.sp = 1;
   /* dynamic shared memory: RTC_SMEM_STACK * BLOCK words (mega_variants) */
   wk.sbase = (uint32_t)__cvta_generic_to_shared(rtc_dyn_smem + threadIdx.x), wk.sstride = 4u * BLOCK;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       if (RESUME && walking)
         wk.resume(ray);
       else
-        wk.begin(alive ? sc.world_root : REF_EMPTY, ray, RTC_INF);
+        wk.begin(alive ? (NW == 4 ? sc.wide_root : sc.world_root) : REF_EMPTY, ray, RTC_INF);
       auto outer = [&]() { return ray; };
       if (RESUME) {
         const int entered = __popc(__ballot_sync(0xffffffffu, !wk.done()));
@@ -580,32 +580,39 @@ struct MegaVariant {
   size_t smem;
   int block;
   int feats; /* FEAT_* mask the kernel was instantiated with: it renders scenes whose mask is a subset */
+  int nw;    /* 2: walks the binary tree; 4: the 4-wide tree (only scenes built with RT_BVH_WIDE=1 have one) */
 };
 #define STACK_SMEM(block) ((size_t)RTC_SMEM_STACK * (block) * sizeof(uint32_t)) /* WalkerT's shared-memory entries */
 static const MegaVariant mega_variants[] = {
-    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK, FEAT_ALL}, /* first entry of an nv = its default */
-    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK, FEAT_ALL},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
-    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
-    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
-    {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL},
-    {-1, 2, mega_render_kernel<2, 512, true, false, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL},
-    {-1, 1, mega_render_kernel<1, 1024, true, false, FEAT_ALL>, STACK_SMEM(1024), 1024, FEAT_ALL},
+    {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK, FEAT_ALL, 2}, /* first entry of an nv = its default */
+    {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK, FEAT_ALL, 2},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
+    {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
+    {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
+    {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL, 2},
+    {-1, 2, mega_render_kernel<2, 512, true, false, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL, 2},
+    {-1, 1, mega_render_kernel<1, 1024, true, false, FEAT_ALL>, STACK_SMEM(1024), 1024, FEAT_ALL, 2},
     /* nv = -2: lockstep CTAs whose trips do not wait for their longest rays (RESUME); nv = -3: the same, free-running */
-    {-2, 2, mega_render_kernel<2, 512, true, true, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL},
-    {-2, 4, mega_render_kernel<4, 256, true, true, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL},
-    {-2, 3, mega_render_kernel<2, 384, true, true, FEAT_ALL>, STACK_SMEM(384), 384, FEAT_ALL}, /* 80 registers */
-    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL},
+    {-2, 2, mega_render_kernel<2, 512, true, true, FEAT_ALL>, STACK_SMEM(512), 512, FEAT_ALL, 2},
+    {-2, 4, mega_render_kernel<4, 256, true, true, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL, 2},
+    {-2, 3, mega_render_kernel<2, 384, true, true, FEAT_ALL>, STACK_SMEM(384), 384, FEAT_ALL, 2}, /* 80 registers */
+    {-3, 8, mega_render_kernel<8, MEGA_BLOCK, false, true, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
     /* LEAN instantiations: the same kernels without the code of what a scene does not contain.  FEATS = 0: spheres
      * with solid-colour lambertian / metal / dielectric / emissive materials (scene 0, Book 1 final); quads + instances
      * + light sampling, no media, no textures (the Cornell box). */
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
-    {0, 10, mega_render_kernel<10, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
-    {0, 12, mega_render_kernel<12, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
+    {0, 10, mega_render_kernel<10, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
+    {0, 12, mega_render_kernel<12, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
     {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>, STACK_SMEM(256), 256,
-     FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS},
+     FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>,
-     STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS},
+     STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
+    /* the three default shapes again, walking the 4-wide tree */
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0, 4>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 4},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 4>,
+     STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 4},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL, 4>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 4},
+    {-2, 2, mega_render_kernel<2, 512, true, true, FEAT_ALL, 4>, STACK_SMEM(512), 512, FEAT_ALL, 4},
 };
 static int env_int(const char *name, int fallback) {
   const char *v = getenv(name);
@@ -618,6 +625,9 @@ static int env_int(const char *name, int fallback) {
  * -3 = free-running + RESUME, 2/4 = warp ray queue) and RT_MEGA_MINB (CTAs per SM the
  * registers must allow) override; a combination that is not built falls back to the nv's first entry. */
 static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int scene_class, int scene_feats) {
+  /* bit 30 of scene_feats: the scene has a 4-wide tree (built with RT_BVH_WIDE=1) and the walk should use it */
+  const int want_nw = (scene_feats & MEGA_FEATS_WIDE_TREE) ? 4 : 2;
+  scene_feats &= ~MEGA_FEATS_WIDE_TREE;
   int nv = env_int("RT_MEGA_NV", -99), minb = env_int("RT_MEGA_MINB", 0);
   if (nv == -99) {
     /* quads without media or textures (the Cornell box): the lean free-running kernel (9 318 Mseg/s) beats the lean
@@ -643,7 +653,7 @@ static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int s
     const MegaVariant *pick = nullptr;
     for (int i = 0; i < n; i++) {
       const MegaVariant &v = mega_variants[i];
-      if (v.nv != want_nv || (pass == 0 && v.minb != minb) || (scene_feats & ~v.feats) != 0)
+      if (v.nv != want_nv || v.nw != want_nw || (pass == 0 && v.minb != minb) || (scene_feats & ~v.feats) != 0)
         continue;
       if (!pick || __builtin_popcount(v.feats) < __builtin_popcount(pick->feats))
         pick = &v;
@@ -651,8 +661,10 @@ static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int s
     if (pick)
       return pick;
   }
+  if (want_nw == 4) /* no wide kernel of that shape is built: the binary walk of the same scene */
+    return mega_variant(cam, n_chunks, scene_class, scene_feats);
   for (int i = 0; i < n; i++)
-    if (mega_variants[i].nv == 0 && mega_variants[i].feats == FEAT_ALL)
+    if (mega_variants[i].nv == 0 && mega_variants[i].feats == FEAT_ALL && mega_variants[i].nw == 2)
       return &mega_variants[i];
   return &mega_variants[0];
 }

@@ -49,6 +49,18 @@ struct __align__(32) BNode {
   uint32_t child0, child1, pad0, pad1;
 };
 
+/* 4-wide node (RT_BVH_WIDE=1, the render kernels' NW = 4 instantiations): the binary tree collapsed two levels at a
+ * time (rtc_bvh.cu: wide_collapse), up to four children with their boxes as (centre, half extent), child k in lane k of
+ * every float4 -- four 256-bit loads per visit for half the visits, half the dependent node fetches and half the votes
+ * of the binary walk.  An absent child has child[k] = REF_EMPTY (its box is never looked at). */
+struct __align__(32) WNode {
+  float4 cx, hx; /* x: centres, half extents of children 0..3 */
+  float4 cy, hy;
+  float4 cz, hz;
+  uint32_t child[4];
+  uint32_t pad[4];
+};
+
 /* sphere as the traversal reads it: one 16-byte load; material/node ids live in a side array */
 struct __align__(16) MSphere {
   float cx, cy, cz, r;
@@ -103,6 +115,8 @@ struct DScene {
   uint32_t objects_root, lights_root;
   /* the rebuilt structure */
   const BNode *bnodes;
+  const WNode *wnodes;   /* the world group's tree again, 4-wide (empty unless the scene was built with RT_BVH_WIDE=1) */
+  uint32_t wide_root;    /* its root reference (an inner reference indexes wnodes), REF_EMPTY: no wide tree */
   const MSphere *msph;
   const MPrimMeta *msph_meta;
   const MQuad *mquads;

@@ -323,7 +323,36 @@ RTC_DEV void leaf_intersect(const DScene &sc, uint32_t ref, const Ray &r, float 
  * changes frame. */
 extern __shared__ __align__(16) uint32_t rtc_dyn_smem[]; /* dynamic shared memory of the render kernels */
 
-template <int SK, int FEATS = FEAT_ALL> struct WalkerT {
+/* the four 32-byte rows of a WNode (render kernels' inlined loops only: see ldg_node on ptxas and 256-bit loads) */
+RTC_DEV void ldg_wnode(const WNode *n, float4 &cx, float4 &hx, float4 &cy, float4 &hy, float4 &cz, float4 &hz,
+                       uint4 &ch) {
+  uint32_t a[8], b[8], c[8], d[8];
+  const char *base = reinterpret_cast<const char *>(n);
+#define RTC_LD256(dst, off)                                                                                          \
+  asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"                                                         \
+      : "=r"(dst[0]), "=r"(dst[1]), "=r"(dst[2]), "=r"(dst[3]), "=r"(dst[4]), "=r"(dst[5]), "=r"(dst[6]),            \
+        "=r"(dst[7])                                                                                                  \
+      : "l"(base + off))
+  RTC_LD256(a, 0);
+  RTC_LD256(b, 32);
+  RTC_LD256(c, 64);
+  RTC_LD256(d, 96);
+#undef RTC_LD256
+#define RTC_F4(v, o) make_float4(__uint_as_float(v[o]), __uint_as_float(v[o + 1]), __uint_as_float(v[o + 2]), __uint_as_float(v[o + 3]))
+  cx = RTC_F4(a, 0), hx = RTC_F4(a, 4), cy = RTC_F4(b, 0), hy = RTC_F4(b, 4), cz = RTC_F4(c, 0), hz = RTC_F4(c, 4);
+#undef RTC_F4
+  ch = make_uint4(d[0], d[1], d[2], d[3]);
+}
+/* order (da, ra), (db, rb) by distance */
+RTC_DEV void wide_cswap(float &da, uint32_t &ra, float &db, uint32_t &rb) {
+  const bool sw = db < da;
+  const float dl = sw ? db : da, dh = sw ? da : db;
+  const uint32_t rl = sw ? rb : ra, rh = sw ? ra : rb;
+  da = dl, db = dh, ra = rl, rb = rh;
+}
+
+template <int SK, int FEATS = FEAT_ALL, int NW = 2> struct WalkerT {
+  static constexpr int kWidth = NW; /* 2: BNode tree (sc.bnodes); 4: WNode tree (sc.wnodes), render kernels only */
   uint32_t *stack;    /* TRACE_STACK entries owned by the caller (a separate local array, so that the scalar members
                          below stay in registers) */
   uint32_t sbase;     /* SK > 0: shared-window address of this lane's column of the CTA's stack (rtc_dyn_smem:
@@ -419,6 +448,44 @@ template <int SK, int FEATS = FEAT_ALL> struct WalkerT {
       next = pop();
     cur = next;
   }
+  /* One 4-wide node (WNode): four box tests, the children that are hit ordered by entry distance (a 5-comparator
+   * network; a miss sorts as +inf), the nearest continued with, the others pushed farthest first.  PARK as in
+   * visit_park: a nearest child that is a leaf goes to the free parking slot and the walk continues with the next. */
+  template <bool NONNEG, bool PARK> RTC_DEV void visit_wide(const DScene &sc, float t_min, uint32_t &parked) {
+    float4 cx, hx, cy, hy, cz, hz;
+    uint4 ch;
+    ldg_wnode(sc.wnodes + cur, cx, hx, cy, hy, cz, hz, ch);
+    float d0, d1, d2, d3;
+    const bool h0 = slab_test<NONNEG>(slab, cx.x, hx.x, cy.x, hy.x, cz.x, hz.x, t_min, best.t, d0);
+    const bool h1 = slab_test<NONNEG>(slab, cx.y, hx.y, cy.y, hy.y, cz.y, hz.y, t_min, best.t, d1);
+    const bool h2 = slab_test<NONNEG>(slab, cx.z, hx.z, cy.z, hy.z, cz.z, hz.z, t_min, best.t, d2) && ch.z != REF_EMPTY;
+    const bool h3 = slab_test<NONNEG>(slab, cx.w, hx.w, cy.w, hy.w, cz.w, hz.w, t_min, best.t, d3) && ch.w != REF_EMPTY;
+    /* (children 0 and 1 always exist: a wide node is made from a binary node's two children) */
+    d0 = h0 ? d0 : RTC_INF, d1 = h1 ? d1 : RTC_INF, d2 = h2 ? d2 : RTC_INF, d3 = h3 ? d3 : RTC_INF;
+    int n = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+    uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
+    wide_cswap(d0, r0, d1, r1), wide_cswap(d2, r2, d3, r3);
+    wide_cswap(d0, r0, d2, r2), wide_cswap(d1, r1, d3, r3);
+    wide_cswap(d1, r1, d2, r2);
+    if (PARK) {
+      const bool park = parked == REF_EMPTY && n > 0 && REF_KIND(r0) != REF_INNER;
+      if (park) {
+        parked = r0;
+        r0 = r1, r1 = r2, r2 = r3;
+        n--;
+      }
+    }
+    if (n > 3)
+      push(r3);
+    if (n > 2)
+      push(r2);
+    if (n > 1)
+      push(r1);
+    uint32_t next = r0;
+    if (n <= 0)
+      next = pop();
+    cur = next;
+  }
   /* one leaf: the primitive is tested in its own frame */
   template <class Outer> RTC_DEV void leaf_test(const DScene &sc, uint32_t ref, float t_min, Outer outer) {
     const uint32_t tag = (FEATS & FEAT_INSTANCES) ? REF_TAG(ref) : 0u;
@@ -489,8 +556,12 @@ RTC_DEV void walk_round_sync(const DScene &sc, W &w, float t_min, Outer outer, i
       const bool in = w.at_inner();
       if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
         break;
-      if (in)
-        w.template visit_park<NONNEG>(sc, t_min, parked); /* parking is part of the visit: no branch of its own */
+      if (in) { /* parking is part of the visit: no branch of its own */
+        if (W::kWidth == 4)
+          w.template visit_wide<NONNEG, true>(sc, t_min, parked);
+        else
+          w.template visit_park<NONNEG>(sc, t_min, parked);
+      }
     }
     if (parked != REF_EMPTY)
       w.leaf_test(sc, parked, t_min, outer);
@@ -500,7 +571,10 @@ RTC_DEV void walk_round_sync(const DScene &sc, W &w, float t_min, Outer outer, i
     const bool in = w.at_inner();
     if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
       break;
-    if (in) { /* (RTC_VISITS_PER_VOTE = 2 halves the votes but measured slower: code size) */
+    if (in && W::kWidth == 4) {
+      uint32_t none = ~REF_EMPTY; /* a parking slot that is never free */
+      w.template visit_wide<NONNEG, false>(sc, t_min, none);
+    } else if (in) { /* (RTC_VISITS_PER_VOTE = 2 halves the votes but measured slower: code size) */
       w.template visit<NONNEG>(sc, t_min);
       if (RTC_VISITS_PER_VOTE > 1 && w.at_inner())
         w.template visit<NONNEG>(sc, t_min);

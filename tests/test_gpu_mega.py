@@ -239,15 +239,16 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
     assert abs(a.mean() - b.mean()) < 2e-3
 
 
-@pytest.mark.parametrize("scene_id", [5, 6, 7])
+@pytest.mark.parametrize("scene_id", [1, 5, 6, 7])
 def test_scene_build_options_agree_bit_for_bit(rtc, scene_factory, scene_id, monkeypatch):
-    """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, and the one-quad-light fast
-    path against the generic walk over world.lights: other structure, other code, the same hits, the same draws --
-    the float radiance must be identical bit for bit."""
+    """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, the one-quad-light fast path
+    against the generic walk over world.lights, the 4-wide tree against the binary one: other structure, other code,
+    the same hits, the same draws -- the float radiance must be identical bit for bit."""
     sess, desc = scene_factory(scene_id, 96, 32)
     opts = rtc.make_opts(kernel="mega", rng="sample")
     results = []
-    for env in ({}, {"RT_BVH_BOXES": "0"}, {"RT_ONE_LIGHT_OFF": "1"}):
+    for env in ({}, {"RT_BVH_BOXES": "1"}, {"RT_ONE_LIGHT_OFF": "1"}, {"RT_BVH_WIDE": "1"},
+                {"RT_BVH_WIDE": "1", "RT_BVH_BOXES": "1"}):
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         scene = rtc.Scene(desc)
