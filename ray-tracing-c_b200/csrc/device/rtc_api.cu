@@ -365,11 +365,14 @@ extern "C" int rt_scene_create(const rt_scene_desc *desc, int device, rt_scene *
   v.objects_root = desc->objects_root;
   v.lights_root = desc->lights_root;
   v.world_root = built.world_root;
+  v.n_pre = built.n_pre, v.pre_ref[0] = built.pre_ref[0], v.pre_ref[1] = built.pre_ref[1];
   v.wide_root = (built.wide_root != REF_EMPTY && built.wide_max_stack + 2 <= TRACE_STACK) ? built.wide_root : REF_EMPTY;
   v.n_media = (uint32_t)built.media.size();
   v.n_perlins = desc->n_perlins;
   v.feats = (built.n_mquads ? FEAT_QUADS : 0) | (built.n_insts ? FEAT_INSTANCES : 0) |
             (desc->lights_root != RT_NONE ? FEAT_LIGHTS : 0) | (built.media.empty() ? 0 : FEAT_MEDIA);
+  if (built.n_pre)
+    v.feats |= FEAT_PRE;
   for (uint32_t k = 0; k < desc->n_textures; k++)
     if (desc->textures[k].kind != RT_TEX_SOLID)
       v.feats |= FEAT_TEXTURES;

@@ -20,6 +20,7 @@ struct BuiltScene {
   std::vector<BNode> bnodes;
   std::vector<WNode> wnodes;         /* world group only, when requested (RT_BVH_WIDE=1) */
   uint32_t wide_root = REF_EMPTY;
+  uint32_t n_pre = 0, pre_ref[2] = {REF_EMPTY, REF_EMPTY}; /* oversized world-group primitives tested before the walk */
   int wide_max_stack = 0;
   std::vector<MSphere> msph;
   std::vector<MPrimMeta> msph_meta;

@@ -276,6 +276,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       else
         wk.begin(alive ? (NW == 4 ? sc.wide_root : sc.world_root) : REF_EMPTY, ray, RTC_INF);
       auto outer = [&]() { return ray; };
+      if ((FEATS & FEAT_PRE) && !(RESUME && walking) && alive)
+        walk_pre(sc, wk, 1e-3f, outer);
       if (RESUME) {
         const int entered = __popc(__ballot_sync(0xffffffffu, !wk.done()));
         const int stop_below = (entered * plan.resume8 + 7) >> 3;
@@ -497,6 +499,7 @@ __global__ void __launch_bounds__(MEGA_BLOCK, MINB)
             if (idle && idx < n_list) {
               mine = smem_bytes[list_base + idx];
               wk.begin(sc.world_root, outer(), RTC_INF);
+              walk_pre(sc, wk, 1e-3f, outer);
             }
             next += __popc(m);
           } else if (m == 0xffffffffu) {
@@ -607,6 +610,10 @@ static const MegaVariant mega_variants[] = {
      FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>,
      STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
+    /* sphere-only worlds with an oversized primitive tested before the walk (FEAT_PRE): lean, and with everything */
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_PRE>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_PRE, 2},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL | FEAT_PRE>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK,
+     FEAT_ALL | FEAT_PRE, 2},
     /* the three default shapes again, walking the 4-wide tree */
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0, 4>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 4},
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 4>,
@@ -641,7 +648,7 @@ static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int s
       minb = scene_class == MEGA_SCENE_MEDIA ? 2 : 4;
   }
   if (env_int("RT_MEGA_LEAN", 1) == 0)
-    scene_feats = FEAT_ALL; /* A/B: only the kernels that carry everything */
+    scene_feats = FEAT_ALL | (scene_feats & FEAT_PRE); /* A/B: only the kernels that carry everything */
   int want_nv = nv;
   /* the slot layout packs the pixel into 16+16 bits, the depth into 16 and the chunk into 8 */
   if (want_nv > 0 && (cam.img_width > 65535 || cam.img_height > 65535 || cam.max_depth > 65535 || n_chunks > 256))
@@ -663,6 +670,11 @@ static const MegaVariant *mega_variant(const rt_camera &cam, int n_chunks, int s
   }
   if (want_nw == 4) /* no wide kernel of that shape is built: the binary walk of the same scene */
     return mega_variant(cam, n_chunks, scene_class, scene_feats);
+  /* no kernel of the requested shape covers the scene's features (a forced RT_MEGA_NV on a FEAT_PRE scene): any
+   * binary-walk kernel that does -- never one that would skip part of the scene */
+  for (int i = 0; i < n; i++)
+    if (mega_variants[i].nw == 2 && mega_variants[i].nv <= 0 && (scene_feats & ~mega_variants[i].feats) == 0)
+      return &mega_variants[i];
   for (int i = 0; i < n; i++)
     if (mega_variants[i].nv == 0 && mega_variants[i].feats == FEAT_ALL && mega_variants[i].nw == 2)
       return &mega_variants[i];

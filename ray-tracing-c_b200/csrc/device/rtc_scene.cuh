@@ -124,6 +124,10 @@ struct DScene {
   const ChainOp *ops;
   const MMedium *media;
   uint32_t world_root, n_media;
+  /* OVERSIZED primitives of the world group (box surface above half of the group's: the r = 1000 ground spheres), kept
+   * out of the tree and tested before every walk (walk_pre): the walk then starts with the t_max they leave, and the
+   * tree has no near-root node whose box is the whole scene */
+  uint32_t n_pre, pre_ref[2];
   uint32_t n_perlins; /* 0: no Perlin texture in the scene (the megakernel skips the warp-wide lookups) */
   /* world.lights is a list of exactly ONE quad (Cornell box, Book 2 final): the quad itself, here in the kernel's
    * parameter space (constant bank, warp-uniform reads), so HittableList_pdf / _rand need no walk over the graph */
@@ -149,6 +153,8 @@ enum {
   FEAT_MEDIA = 8,      /* ConstantMedium items (and their isotropic phase functions) */
   FEAT_TEXTURES = 16,  /* any texture that is not a solid colour (checker, image, Perlin) */
   FEAT_ALL = 31,
+  FEAT_PRE = 32,       /* oversized primitives tested before the walk (DScene.pre_ref): sphere-only worlds; NOT part
+                          of FEAT_ALL -- the kernels of the other scenes carry none of its code */
 };
 
 /* material.h:10-18 plus the id of the node that produced the hit */

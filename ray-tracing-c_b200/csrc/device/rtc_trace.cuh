@@ -530,6 +530,14 @@ template <int SK, int FEATS = FEAT_ALL, int NW = 2> struct WalkerT {
 };
 typedef WalkerT<0> Walker; /* the whole stack in the caller's local array */
 
+/* The world group's oversized primitives (DScene.pre_ref), tested right after begin() of a walk over that group. */
+template <class W, class Outer> RTC_DEV void walk_pre(const DScene &sc, W &w, float t_min, Outer outer) {
+  if (sc.n_pre > 0u)
+    w.leaf_test(sc, sc.pre_ref[0], t_min, outer);
+  if (sc.n_pre > 1u)
+    w.leaf_test(sc, sc.pre_ref[1], t_min, outer);
+}
+
 /* One round of a WARP-SYNCHRONOUS walk (all 32 lanes call it together, a lane without a ray with w.done()):
  * descend while at least `thr8` eighths of the warp's busy lanes hold an inner node, then the lanes that hold a leaf
  * process it.  thr8 = 0 is the classic "while-while" (descend while ANY lane holds an inner node): there one lane on
@@ -557,10 +565,13 @@ RTC_DEV void walk_round_sync(const DScene &sc, W &w, float t_min, Outer outer, i
       if (__popc(__ballot_sync(0xffffffffu, in)) < thr)
         break;
       if (in) { /* parking is part of the visit: no branch of its own */
-        if (W::kWidth == 4)
+        if (W::kWidth == 4) {
           w.template visit_wide<NONNEG, true>(sc, t_min, parked);
-        else
+        } else {
           w.template visit_park<NONNEG>(sc, t_min, parked);
+          if (RTC_VISITS_PER_VOTE > 1 && w.at_inner()) /* a second visit under the same vote (A/B: -DRTC_VISITS_PER_VOTE=2) */
+            w.template visit_park<NONNEG>(sc, t_min, parked);
+        }
       }
     }
     if (parked != REF_EMPTY)
@@ -587,12 +598,15 @@ RTC_DEV void walk_round_sync(const DScene &sc, W &w, float t_min, Outer outer, i
 /* Closest hit in the group rooted at `root` for the ray `r` (given in the group's frame), one ray per lane.
  * "while-while": all lanes of a warp first descend inner nodes together until each holds a leaf (or is done), then
  * all process leaves together -- keeps the 32 lanes in the same code far more often than one if/else per step. */
+template <bool WORLD = false> /* WORLD: `root` is the world group's: its oversized primitives are tested first */
 RTC_DEV TraceHit trace_group(const DScene &sc, uint32_t root, const Ray &r, float t_min, float t_max) {
   uint32_t stack[TRACE_STACK];
   Walker w;
   w.stack = stack;
   w.begin(root, r, t_max);
   auto outer = [&]() { return r; };
+  if (WORLD)
+    walk_pre(sc, w, t_min, outer);
   for (;;) {
     while (w.at_inner())
       w.visit<false>(sc, t_min);
@@ -656,6 +670,7 @@ static __device__ __noinline__ float trace_early_call(const DScene &sc, const Ra
   w.stack = stack;
   w.begin(sc.world_root, r, t_max);
   auto outer = [&]() { return r; };
+  /* (no oversized primitives to look at here: rtc_bvh.cu only takes them out of the tree in worlds without media) */
   for (;;) {
     while (w.at_inner())
       w.visit<false>(sc, t_min);
@@ -850,7 +865,7 @@ RTC_DEV void trace_finalize(const DScene &sc, const Ray &world, const TraceHit &
 
 /* The integrator's query (raytracing.c:45): surfaces, then media. */
 template <bool EXACT> RTC_DEV TraceHit trace_world(const DScene &sc, const Ray &world, float t_min, float t_max, Rng &g) {
-  TraceHit best = trace_group(sc, sc.world_root, world, t_min, t_max);
+  TraceHit best = trace_group<true>(sc, sc.world_root, world, t_min, t_max);
   if (sc.n_media)
     trace_media<EXACT>(sc, world, t_min, best, g);
   return best;

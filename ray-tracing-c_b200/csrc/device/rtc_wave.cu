@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(WAVE_BLOCK)
     const float4 o = pool.o_bx[slot], d = pool.d_by[slot];
     Ray ray;
     ray.o = v3(o.x, o.y, o.z), ray.d = v3(d.x, d.y, d.z);
-    TraceHit th = trace_group(sc, sc.world_root, ray, 1e-3f, RTC_INF);
+    TraceHit th = trace_group<true>(sc, sc.world_root, ray, 1e-3f, RTC_INF);
     if (sc.n_media) { /* the medium's free-path draw comes from the path's own stream */
       const uint4 rs = pool.rng[slot];
       Rng rng = rng_unpack(rs);

@@ -201,7 +201,12 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
     """Free-running, lockstep-CTA and warp-ray-queue kernels, voted and plain node loops: the schedule of the work
     changes, the arithmetic of a sample and the order in which a work item sums its samples do not -- so the float
     radiance must be identical bit for bit, and so must the segment counts."""
-    sess, desc, scene = gpu_scene(scene_id, 96, 32)
+    # (RT_BVH_PRE=0: a scene with an oversized primitive outside its tree can only be rendered by the kernels
+    # instantiated for that, and every forced shape would silently fall back to them)
+    monkeypatch.setenv("RT_BVH_PRE", "0")
+    sess, desc, _ = gpu_scene(scene_id, 96, 32)
+    scene = rtc.Scene(desc)
+    monkeypatch.delenv("RT_BVH_PRE")
     opts = rtc.make_opts(kernel="mega", rng="sample")
     monkeypatch.setenv("RT_MEGA_CHUNKS", "2")  # same chunking for every variant
     monkeypatch.setenv("RT_MEGA_LEAN", "0")    # ... and the same instantiation (all features) of every kernel shape
@@ -237,18 +242,20 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
     a, b = np.clip(rad_l / 32, 0, 1), np.clip(rad_f / 32, 0, 1)
     assert np.sqrt(((a - b) ** 2).mean()) < 0.03
     assert abs(a.mean() - b.mean()) < 2e-3
+    scene.close()
 
 
-@pytest.mark.parametrize("scene_id", [1, 5, 6, 7])
+@pytest.mark.parametrize("scene_id", [0, 1, 4, 5, 6, 7])
 def test_scene_build_options_agree_bit_for_bit(rtc, scene_factory, scene_id, monkeypatch):
     """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, the one-quad-light fast path
-    against the generic walk over world.lights, the 4-wide tree against the binary one: other structure, other code,
+    against the generic walk over world.lights, the 4-wide tree against the binary one, oversized primitives tested
+    before the walk against the same primitives inside the tree (scenes 0, 1, 4: ground spheres): other structure, other code,
     the same hits, the same draws -- the float radiance must be identical bit for bit."""
     sess, desc = scene_factory(scene_id, 96, 32)
     opts = rtc.make_opts(kernel="mega", rng="sample")
     results = []
     for env in ({}, {"RT_BVH_BOXES": "1"}, {"RT_ONE_LIGHT_OFF": "1"}, {"RT_BVH_WIDE": "1"},
-                {"RT_BVH_WIDE": "1", "RT_BVH_BOXES": "1"}):
+                {"RT_BVH_WIDE": "1", "RT_BVH_BOXES": "1"}, {"RT_BVH_PRE": "0"}, {"RT_BVH_PRE": "0", "RT_BVH_WIDE": "1"}):
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         scene = rtc.Scene(desc)
