@@ -186,6 +186,11 @@ inline uint64_t mix64(uint64_t h, uint64_t v, uint64_t mul) {
   return h ^ (h >> 29);
 }
 void hash_bytes(const void *data, size_t bytes, uint64_t key[2]) {
+  if (data == nullptr)
+    bytes = 0; /* an empty array of the description (its pointer may be NULL): only the length goes in */
+  static const uint8_t nothing[32] = {0};
+  if (bytes == 0)
+    data = nothing;
   /* four independent lanes over 32-byte blocks (a single multiply chain would be latency-bound: the image texture
    * of the Book 2 scene alone is 1.5 MB), folded into two 64-bit words */
   const uint8_t *p = static_cast<const uint8_t *>(data);
@@ -219,6 +224,15 @@ void hash_desc(const rt_scene_desc &d, uint64_t key[2]) {
   hash_bytes(d.perlins, sizeof(rt_perlin) * d.n_perlins, key);
   hash_bytes(d.images, sizeof(rt_image) * d.n_images, key);
   hash_bytes(d.texels, d.n_texel_bytes, key);
+  /* what rt_scene_create builds also depends on these build-time knobs: a scene built under one setting must not be
+   * handed out under another */
+  static const char *const knobs[] = {"RT_BVH_BOXES", "RT_BVH_WIDE", "RT_BVH_PRE", "RT_BVH_COST_SPHERE",
+                                      "RT_BVH_COST_QUAD", "RT_BVH_COST_BOX", "RT_ONE_LIGHT_OFF", "RT_CONST_CHAINS_OFF"};
+  for (const char *name : knobs) {
+    const char *v = getenv(name);
+    hash_bytes(name, strlen(name), key);
+    hash_bytes(v ? v : "", v ? strlen(v) : 0, key);
+  }
 }
 } // namespace
 
@@ -797,11 +811,18 @@ void multi_teardown() {
   m = MultiContext();
 }
 
+int multi_setup_fresh(int n_gpus);
 int multi_setup(int n_gpus) {
-  MultiContext &m = g_multi;
-  if (m.n == n_gpus)
+  if (g_multi.n == n_gpus)
     return RT_OK;
   multi_teardown();
+  const int rc = multi_setup_fresh(n_gpus);
+  if (rc != RT_OK)
+    multi_teardown(); /* a half-made context must not look complete to the next call */
+  return rc;
+}
+int multi_setup_fresh(int n_gpus) {
+  MultiContext &m = g_multi;
   m.streams.assign(n_gpus, nullptr), m.done.assign(n_gpus, nullptr), m.comms.assign(n_gpus, nullptr);
   m.n = n_gpus;
   for (int g = 0; g < n_gpus; g++) {

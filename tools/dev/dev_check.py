@@ -1,5 +1,5 @@
 """Developer diagnostic (not a pytest file): runs every scene through the exact and mega kernels on cuda:0 and
-prints how they compare with the CPU oracle.  `python tests/dev_check.py [scene ...]`"""
+prints how they compare with the CPU oracle.  `python tools/dev/dev_check.py [scene ...]`"""
 from __future__ import annotations
 
 import importlib
@@ -9,7 +9,7 @@ from pathlib import Path
 
 import numpy as np
 
-ROOT = Path(__file__).resolve().parent.parent
+ROOT = Path(__file__).resolve().parent.parent.parent
 sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
