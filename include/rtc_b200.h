@@ -251,6 +251,8 @@ typedef struct rt_scene_info {
   int32_t light_nesting;  /* lists under world.lights; -1 = a list nothing can be sampled from */
   uint32_t mega_supported;
   uint64_t device_bytes;  /* bytes rt_scene_create uploads */
+  uint32_t pre_prims;     /* oversized primitives kept out of the tree and tested before every walk (0..2) */
+  uint32_t wide_nodes;    /* nodes of the 4-wide tree (0 unless built with RT_BVH_WIDE=1) */
 } rt_scene_info;
 int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info);
 

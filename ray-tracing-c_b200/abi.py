@@ -105,14 +105,15 @@ class rt_scene_info(C.Structure):
         ("bvh_nodes", C.c_uint32), ("bvh_depth", C.c_uint32), ("spheres", C.c_uint32), ("quads", C.c_uint32),
         ("instances", C.c_uint32), ("media", C.c_uint32), ("chain_ops", C.c_uint32), ("graph_frames", C.c_uint32),
         ("graph_rays", C.c_uint32), ("graph_recs", C.c_uint32), ("light_nesting", C.c_int32),
-        ("mega_supported", C.c_uint32), ("device_bytes", C.c_uint64),
+        ("mega_supported", C.c_uint32), ("device_bytes", C.c_uint64), ("pre_prims", C.c_uint32),
+        ("wide_nodes", C.c_uint32),
     ]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
-assert C.sizeof(rt_scene_info) == 56
+assert C.sizeof(rt_scene_info) == 64
 assert C.sizeof(rt_scene_desc) == 128 and C.sizeof(rt_camera) == 128 and C.sizeof(rt_opts) == 32
 assert C.sizeof(rt_stats) == 48
 

@@ -448,11 +448,13 @@ extern "C" int rt_scene_inspect(const rt_scene_desc *desc, rt_scene_info *info) 
   info->graph_recs = (uint32_t)b.graph_recs;
   info->light_nesting = b.light_nesting;
   info->mega_supported = b.mega_supported && b.max_stack + 2 <= TRACE_STACK;
+  info->pre_prims = b.n_pre;
+  info->wide_nodes = b.wide_root != REF_EMPTY && REF_KIND(b.wide_root) == REF_INNER ? (uint32_t)b.wnodes.size() : 0u;
   info->device_bytes = sizeof(rt_node) * desc->n_nodes + 4ull * desc->n_children + sizeof(rt_sphere) * desc->n_spheres +
                        sizeof(rt_quad) * desc->n_quads + sizeof(rt_material) * desc->n_materials +
                        sizeof(rt_texture) * desc->n_textures + sizeof(rt_perlin) * desc->n_perlins +
                        sizeof(rt_image) * desc->n_images + desc->n_texel_bytes + sizeof(BNode) * b.bnodes.size() +
-                       (sizeof(MSphere) + sizeof(MPrimMeta)) * b.msph.size() + sizeof(MQuad) * b.mquads.size() +
+                       (b.wide_root != REF_EMPTY ? sizeof(WNode) * b.wnodes.size() : 0) + (sizeof(MSphere) + sizeof(MPrimMeta)) * b.msph.size() + sizeof(MQuad) * b.mquads.size() +
                        sizeof(Instance) * b.insts.size() + sizeof(ChainOp) * b.ops.size() +
                        sizeof(MMedium) * b.media.size();
   return RT_OK;

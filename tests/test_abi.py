@@ -204,3 +204,27 @@ def test_write_tiff_bytes_equal_the_reference_writer(rtc, tmp_path, name, shape)
     assert host.write_tiff(f, w, h, c, px.ctypes.data_as(C.c_void_p)) == 0
     libc.fclose(f)
     assert path.read_bytes() == want
+
+
+def test_builder_options_are_visible_to_inspect(rtc, scene_factory, monkeypatch):
+    """rt_scene_inspect (host only) reports what the two optional builder steps did: oversized primitives taken out of
+    the tree of a sphere-only world (the ground spheres of scenes 0 and 1; never in worlds with quads or media, never
+    when fewer than two primitives would stay: the two equal spheres of scene 2, ground + marble ball of scene 4), and the 4-wide tree under
+    RT_BVH_WIDE=1 (each wide node replaces one to three binary ones)."""
+    want_pre = {0: 1, 1: 1, 2: 0, 4: 0, 5: 0, 6: 0, 7: 0}
+    for scene_id, n_pre in want_pre.items():
+        _, desc = scene_factory(scene_id, 48, 4)
+        info = rtc.inspect(desc)
+        assert info["pre_prims"] == n_pre, (scene_id, info)
+        assert info["wide_nodes"] == 0
+        plain_nodes = info["bvh_nodes"]
+        monkeypatch.setenv("RT_BVH_PRE", "0")
+        off = rtc.inspect(desc)
+        monkeypatch.delenv("RT_BVH_PRE")
+        assert off["pre_prims"] == 0 and off["bvh_nodes"] == plain_nodes + n_pre  # one leaf = one more binary node
+        monkeypatch.setenv("RT_BVH_WIDE", "1")
+        wide = rtc.inspect(desc)
+        monkeypatch.delenv("RT_BVH_WIDE")
+        if plain_nodes > 0:
+            assert 0 < wide["wide_nodes"] <= plain_nodes and 3 * wide["wide_nodes"] >= plain_nodes
+        assert wide["bvh_nodes"] == plain_nodes and wide["mega_supported"] == 1

@@ -249,7 +249,7 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
 def test_scene_build_options_agree_bit_for_bit(rtc, scene_factory, scene_id, monkeypatch):
     """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, the one-quad-light fast path
     against the generic walk over world.lights, the 4-wide tree against the binary one, oversized primitives tested
-    before the walk against the same primitives inside the tree (scenes 0, 1, 4: ground spheres): other structure, other code,
+    before the walk against the same primitives inside the tree (scenes 0, 1: ground spheres): other structure, other code,
     the same hits, the same draws -- the float radiance must be identical bit for bit."""
     sess, desc = scene_factory(scene_id, 96, 32)
     opts = rtc.make_opts(kernel="mega", rng="sample")
