@@ -740,6 +740,18 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
     plan->n_chunks = c;
     plan->chunk = plan->begin[1] - plan->begin[0];
   }
+  /* every work item of a pixel owns one partial-sum frame: never more than 8 GiB of them (a 4K frame at 4096 spp
+   * uses 33 = 3.3 GB; an 8K x 8K frame would ask for 26 GB) -- the trailing items are merged into the last one */
+  if (plan->n_chunks > 2 && pixels > 0) {
+    const long long frame_bytes = pixels * 3 * (long long)sizeof(float);
+    long long fit = (8ll << 30) / frame_bytes;
+    if (fit < 2)
+      fit = 2;
+    if ((long long)plan->n_chunks > fit) {
+      plan->n_chunks = (int)fit;
+      plan->begin[plan->n_chunks] = sample_count;
+    }
+  }
   plan->partial_bytes = plan->n_chunks > 1 ? (size_t)plan->n_chunks * (size_t)pixels * 3 * sizeof(float) : 0;
   if (mega_variant(cam, plan->n_chunks, scene_class, scene_feats) != var) { /* capacity check failed: the register kernel */
     var = mega_variant(cam, plan->n_chunks, scene_class, scene_feats);
