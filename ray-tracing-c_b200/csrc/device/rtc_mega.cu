@@ -29,6 +29,7 @@
 #define MEGA_BLOCK 128
 #define MEGA_THR8_DEFAULT 2 /* measured: see DESIGN.md */
 #define MEGA_CTA8_DEFAULT 3 /* measured on Book 2 final: 3 +6 %, 4 +5.6 %, 6 +3.3 %, 7 +1.9 % (0 = off) */
+#define MEGA_GUIDED_DEFAULT 4 /* a work item = a quarter of the samples its pixel has left (mega_plan) */
 #define MEGA_RESUME8_DEFAULT 1 /* measured on Book 2 final: 1 +1.7 %, 2 +0.6 %, 3 -3 %, 4 -7 % */
 
 RTC_DEV bool has_nan3(V3 a) { return a.x != a.x || a.y != a.y || a.z != a.z; }
@@ -727,12 +728,15 @@ cudaError_t mega_plan(const rt_camera &cam, int sample_count, uint32_t rng_mode,
    * median CTA done at 25.2 ms and the last one at 27.3 ms.  So an item takes a QUARTER of the samples its pixel has
    * left (at least one): whatever an expensive pixel's item costs, three times as much work is still to be handed out
    * behind it.  The chunks are still summed in order (mega_sum_chunks_kernel): images stay deterministic. */
-  if (n_chunks > 1 && env_int("RT_MEGA_GUIDED", 1) != 0 && env_int("RT_MEGA_CHUNKS", 0) <= 0) {
+  int guided = env_int("RT_MEGA_GUIDED", MEGA_GUIDED_DEFAULT); /* 0: equal items; d >= 2: an item = 1/d of the rest */
+  if (guided == 1)
+    guided = MEGA_GUIDED_DEFAULT;
+  if (n_chunks > 1 && guided >= 2 && env_int("RT_MEGA_CHUNKS", 0) <= 0) {
     int c = 0, at = 0;
     while (at < sample_count && c < MEGA_MAX_CHUNKS - 1) {
       plan->begin[c++] = at;
       const int left = sample_count - at;
-      at += left / 4 > 1 ? left / 4 : 1;
+      at += left / guided > 1 ? left / guided : 1;
     }
     if (at < sample_count) /* (more than 64 items are never needed below ~1e8 samples; the last one takes the rest) */
       plan->begin[c++] = at;
