@@ -265,7 +265,11 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, flo
               rt_stats *stats);
 
 /* Same render into a DEVICE buffer float[h][w][3] (overwritten, not accumulated), asynchronous on `cuda_stream`
- * (a cudaStream_t, NULL = default stream).  For one-process-per-GPU drivers that reduce with NCCL afterwards. */
+ * (a cudaStream_t, NULL = default stream).  For one-process-per-GPU drivers that reduce with NCCL afterwards.
+ * Asynchronous for RT_KERNEL_MEGA and RT_KERNEL_EXACT only: RT_KERNEL_WAVE polls its live-path count from the host
+ * between batches of iterations, i.e. it SYNCHRONISES `cuda_stream` (idle on return), and fails with RT_ERR_CUDA
+ * (launch timeout) instead of returning an incomplete frame if its iteration bound runs out.  The first call on a
+ * scene (or a larger frame) may allocate scratch from the stream-ordered pool; rt_render_device_noalloc never does. */
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_opts *opts, float *radiance_sum_dev,
                      void *cuda_stream);
 /* rt_render_device WITHOUT ANY ALLOCATION, for callers that cannot call cudaMalloc (code under CUDA graph capture,
