@@ -40,6 +40,9 @@
 #ifndef RTC_MEDIA_INLIST
 #define RTC_MEDIA_INLIST 1 /* 0: media clipped against the closest surface whatever its list position (round 1) */
 #endif
+#ifndef RTC_NODE_LD_HINT
+#define RTC_NODE_LD_HINT "" /* L1 eviction priority of the node loads, e.g. ".L1::evict_last" (A/B: no gain) */
+#endif
 #ifndef RTC_CONST_CHAINS
 #define RTC_CONST_CHAINS 1
 #endif
@@ -113,10 +116,10 @@ static __device__ __noinline__ void chain_unapply_call(const DScene &sc, uint32_
 template <bool WIDE> RTC_DEV void ldg_node(const BNode *n, float4 &xy0, float4 &xy1, float4 &zz, uint2 &ch) {
   if (WIDE) {
     uint32_t a0, a1, a2, a3, a4, a5, a6, a7, b0, b1, b2, b3, pad0, pad1;
-    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm("ld.global.nc" RTC_NODE_LD_HINT ".v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3), "=r"(a4), "=r"(a5), "=r"(a6), "=r"(a7)
         : "l"(n));
-    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm("ld.global.nc" RTC_NODE_LD_HINT ".v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3), "=r"(ch.x), "=r"(ch.y), "=r"(pad0), "=r"(pad1)
         : "l"(reinterpret_cast<const char *>(n) + 32));
     xy0 = make_float4(__uint_as_float(a0), __uint_as_float(a1), __uint_as_float(a2), __uint_as_float(a3));
