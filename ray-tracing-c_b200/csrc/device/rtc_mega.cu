@@ -65,13 +65,40 @@ RTC_DEV Frame frame_of(const DScene &sc, const RenderJob &job, const MegaPlan &p
   return f;
 }
 
-/* Fetches the next work item that lies inside the image.  false = no items left. */
+/* A word of per-lane state: a register, or (COLD) one slot of shared memory -- for what no traversal touches (the
+ * sample sums of the work item, the launch counters), so that the node loop has the registers to itself. */
+template <bool COLD, typename T> struct Kept {
+  T reg;
+  volatile T *mem;
+  RTC_DEV explicit Kept(T *slot) : reg(0), mem(slot) {
+    if (COLD)
+      *mem = 0;
+  }
+  RTC_DEV T get() const { return COLD ? *mem : reg; }
+  RTC_DEV void set(T v) {
+    if (COLD)
+      *mem = v;
+    else
+      reg = v;
+  }
+  RTC_DEV void add(T v) { set(get() + v); } /* float: one rounded addition either way (no product to contract) */
+};
+
+/* Fetches the next work item that lies inside the image.  false = no items left.  (The kernels built with POOL draw
+ * 32 items per warp instead, mega_render_kernel.) */
+/* RTC_ITEM_POOL: -1 = as the variant table says, 0 / 1 = every kernel without / with the warp pool (A/B builds) */
+#ifndef RTC_ITEM_POOL
+#define RTC_ITEM_POOL -1
+#endif
 RTC_DEV bool fetch_item(const Frame &f, const RenderJob &job, int &pi, int &pj, int &chunk_id) {
   for (;;) {
     unsigned item = atomicAdd(&job.counters->next_item, 1u);
     if (item >= f.n_items)
       return false;
     unsigned c = item / (f.tiles * 32u), pix = item - c * (f.tiles * 32u);
+#ifdef RTC_SCRAMBLE /* measurement only: consecutive items are pixels of 32 different tiles (how much is coherence worth?) */
+    pix = (pix % 32u) * f.tiles + pix / 32u;
+#endif
     item_to_pixel(pix, f.w, f.h, pi, pj);
     if (pi >= f.w || pj >= f.h)
       continue; /* padding of the last tile column / row */
@@ -187,13 +214,36 @@ RTC_DEV void flush_counters(const RenderJob &job, unsigned n_segments, unsigned 
  * issues of a warp there): once plan.cta8/8 of the CTA's warps have finished the trip's traversal, the others suspend
  * theirs too (after at least one round, so every trip makes progress; warps without work do not count, so nobody is
  * suspended when few warps have work left). */
-template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS, int NW = 2>
+/* POOL: the warp draws 32 consecutive items at a time -- one chunk of the 32 pixels of ONE tile -- and hands them to its
+ * lanes as they come free.  With one draw per lane the lanes of a warp drift to 32 unrelated pixels after their first
+ * item; with the pool they stay on one or two tiles (coherent camera rays, shared nodes), and the counter is hit once per
+ * 32 items.  Measured (tools/gpu_run27.sh, gpu_run28.sh): items scattered over 32 tiles from the start
+ * cost Book 1 final +7 %; the pool gains it 6.2 % at 125 and at 1000 spp, the Cornell box 1.6-2.0 %, scene 0 2.5 %; the
+ * lockstep kernels lose 0.3-1.9 % (Book 2 final, the quad scene), so they keep the per-lane draw.
+ * COLD: the sample sums and the launch counters live in shared memory (Kept).  tools/gpu_run26.sh: the Cornell box
+ * -1.8 %, the free-running all-features kernel -1.4..-2.0 % (scenes 2, 5); Book 1 final +3.6 %, Book 2 final +1.0 %,
+ * the 256-thread lockstep kernel +-0: built where it pays. */
+template <int MINB, int BLOCK, bool LOCKSTEP, bool RESUME, int FEATS, int NW = 2, bool COLD = false, bool POOL_ = false>
 __global__ void __launch_bounds__(BLOCK, MINB)
     mega_render_kernel(const __grid_constant__ DScene sc, const __grid_constant__ RenderJob job,
                        const __grid_constant__ MegaPlan plan, float *partial) {
+  constexpr bool POOL = RTC_ITEM_POOL < 0 ? POOL_ : RTC_ITEM_POOL != 0;
   const Frame f = frame_of(sc, job, plan);
   /* per-lane counts of one launch: a lane would need days to overflow 32 bits */
-  unsigned n_segments = 0, n_pdf = 0, n_samples = 0, n_nan = 0;
+  /* COLD: these seven words live in shared memory, [field][thread] (every access one conflict-free ld/st.shared) */
+  __shared__ unsigned cold_u[COLD ? 4 : 1][COLD ? BLOCK : 1];
+  __shared__ float cold_f[COLD ? 3 : 1][COLD ? BLOCK : 1];
+  const int cold_t = COLD ? (int)threadIdx.x : 0;
+  /* POOL: the warp's drawn and not yet handed-out items [next, end) */
+  __shared__ volatile unsigned pool_w[2][POOL ? BLOCK / 32 : 1];
+  if (POOL) {
+    if ((threadIdx.x & 31u) == 0)
+      pool_w[0][threadIdx.x >> 5] = pool_w[1][threadIdx.x >> 5] = 0;
+    __syncwarp();
+  }
+  Kept<COLD, unsigned> n_segments(&cold_u[0][cold_t]), n_pdf(&cold_u[COLD ? 1 : 0][cold_t]),
+      n_samples(&cold_u[COLD ? 2 : 0][cold_t]), n_nan(&cold_u[COLD ? 3 : 0][cold_t]);
+  Kept<COLD, float> sum_x(&cold_f[0][cold_t]), sum_y(&cold_f[COLD ? 1 : 0][cold_t]), sum_z(&cold_f[COLD ? 2 : 0][cold_t]);
 #ifdef RTC_TIMELINE /* development build: when does every CTA start, run out of items, and end? */
   unsigned long long tl_in = 0, tl_dry = 0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_in));
@@ -204,7 +254,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   rng.state = 0, rng.inc = 1;
   Ray ray;
   ray.o = ray.d = v3(0, 0, 0);
-  V3 beta = v3(1, 1, 1), sum = v3(0, 0, 0);
+  V3 beta = v3(1, 1, 1);
   int pi = 0, pj = 0, s = 0, depth = 0, chunk_id = 0;
   bool have_item = false, alive = false;
   /* the traversal state outlives a trip only in the RESUME kernels */
@@ -229,18 +279,67 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   bool done = false; /* this lane has no work left; it stays in the loop (idle) until its whole warp is done */
   for (;; trip++) {
     /* ---- phase 1: regenerate.  Lanes whose path ended take the next sample of their item or fetch a new item. */
+    if (POOL) {
+      /* finished chunks are stored, then the lanes without an item are served from the warp's pool, lowest lane first */
+      bool need = !alive && !done;
+      if (need && have_item) {
+        if (s == job.sample_begin + min(plan_chunk_begin(plan, chunk_id + 1), job.sample_count)) {
+          float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
+                       ((size_t)pj * f.w + pi) * 3;
+          dst[0] = sum_x.get(), dst[1] = sum_y.get(), dst[2] = sum_z.get();
+          have_item = false;
+        }
+      }
+      need = need && !have_item;
+      const unsigned lane_id = threadIdx.x & 31u, warp_id = threadIdx.x >> 5;
+      unsigned need_mask = __ballot_sync(0xffffffffu, need);
+      while (need_mask) {
+        unsigned next = pool_w[0][warp_id], end = pool_w[1][warp_id];
+        if (next == end) {
+          unsigned base = 0;
+          if (lane_id == 0)
+            base = atomicAdd(&job.counters->next_item, 32u);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (base >= f.n_items) { /* n_items is a multiple of 32: nothing left for anybody */
+            if (need)
+              done = true;
+            break;
+          }
+          next = base, end = base + 32u;
+        }
+        const unsigned rank = __popc(need_mask & ((1u << lane_id) - 1u));
+        if (need && rank < end - next) {
+          const unsigned item = next + rank, c = item / (f.tiles * 32u), pix = item - c * (f.tiles * 32u);
+          item_to_pixel(pix, f.w, f.h, pi, pj);
+          if (pi < f.w && pj < f.h) { /* else: padding of the last tile column / row, the lane asks again */
+            chunk_id = (int)c;
+            s = job.sample_begin + plan_chunk_begin(plan, chunk_id);
+            sum_x.set(0.0f), sum_y.set(0.0f), sum_z.set(0.0f);
+            if (job.rng_mode == RT_RNG_PIXEL)
+              rng_seed_pixel(rng, pi, pj);
+            have_item = true, need = false;
+          }
+        }
+        next += min(end - next, (unsigned)__popc(need_mask));
+        __syncwarp();
+        if (lane_id == 0)
+          pool_w[0][warp_id] = next, pool_w[1][warp_id] = end;
+        __syncwarp();
+        need_mask = __ballot_sync(0xffffffffu, need);
+      }
+    }
     if (!alive && !done) {
-      if (have_item && s == job.sample_begin + min(plan_chunk_begin(plan, chunk_id + 1), job.sample_count)) {
+      if (!POOL && have_item && s == job.sample_begin + min(plan_chunk_begin(plan, chunk_id + 1), job.sample_count)) {
         /* chunk finished: one store per item */
         float *dst = (plan.n_chunks > 1 ? partial + (size_t)chunk_id * (size_t)f.w * f.h * 3 : job.radiance) +
                      ((size_t)pj * f.w + pi) * 3;
-        dst[0] = sum.x, dst[1] = sum.y, dst[2] = sum.z;
+        dst[0] = sum_x.get(), dst[1] = sum_y.get(), dst[2] = sum_z.get();
         have_item = false;
       }
-      if (!have_item) {
+      if (!POOL && !have_item) {
         if (fetch_item(f, job, pi, pj, chunk_id)) {
           s = job.sample_begin + plan_chunk_begin(plan, chunk_id);
-          sum = v3(0, 0, 0);
+          sum_x.set(0.0f), sum_y.set(0.0f), sum_z.set(0.0f);
           if (job.rng_mode == RT_RNG_PIXEL)
             rng_seed_pixel(rng, pi, pj);
           have_item = true;
@@ -259,7 +358,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
         beta = v3(1, 1, 1);
         depth = 0;
         alive = f.max_depth > 0;
-        n_samples++;
+        n_samples.add(1u);
         if (!alive)
           s++; /* depth 0: the sample contributes nothing (raytracing.c:40-41) */
       }
@@ -311,7 +410,7 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       th = wk.best;
     }
     if (alive && !(RESUME && walking)) {
-      n_segments++;
+      n_segments.add(1u);
       if ((FEATS & FEAT_MEDIA) && sc.n_media)
         trace_media<false>(sc, ray, 1e-3f, th, rng);
     }
@@ -325,25 +424,28 @@ __global__ void __launch_bounds__(BLOCK, MINB)
     V3 L = v3(0, 0, 0);
     PendingTex pend;
     pend.tex = RT_NONE;
+    unsigned pdf_now = 0;
     if (alive && !(RESUME && walking) &&
-        shade_segment<true, FEATS>(sc, f, th, ray, beta, L, depth, rng, n_pdf, pend)) {
+        shade_segment<true, FEATS>(sc, f, th, ray, beta, L, depth, rng, pdf_now, pend)) {
       alive = false;
       s++;
       if (has_nan3(L)) {
-        n_nan++;
+        n_nan.add(1u);
         if (!(job.flags & RT_FLAG_DROP_NAN))
-          sum = v_add(sum, L);
+          sum_x.add(L.x), sum_y.add(L.y), sum_z.add(L.z);
       } else {
-        sum = v_add(sum, L);
+        sum_x.add(L.x), sum_y.add(L.y), sum_z.add(L.z);
       }
     }
+    if (pdf_now)
+      n_pdf.add(pdf_now);
     /* Perlin albedos owed by this trip's hits: evaluated by the whole warp, one lookup after the other (the point is the
      * scattered ray's origin; a path that ended at max_depth owes one too, its throughput is not used again) */
     if ((FEATS & FEAT_TEXTURES) && sc.n_perlins)
       perlin_settle_warp(sc, pend.tex, ray.o, beta);
   }
   /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
-  flush_counters(job, n_segments, n_pdf, n_samples, n_nan);
+  flush_counters(job, n_segments.get(), n_pdf.get(), n_samples.get(), n_nan.get());
 #ifdef RTC_TIMELINE
   if (threadIdx.x == 0) {
     unsigned long long tl_out;
@@ -590,7 +692,8 @@ struct MegaVariant {
 static const MegaVariant mega_variants[] = {
     {2, 6, mega_queue_kernel<6, 2>, mega_queue_smem<2>(), MEGA_BLOCK, FEAT_ALL, 2}, /* first entry of an nv = its default */
     {4, 4, mega_queue_kernel<4, 4>, mega_queue_smem<4>(), MEGA_BLOCK, FEAT_ALL, 2},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL, 2, true>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK,
+     FEAT_ALL, 2},
     {0, 6, mega_render_kernel<6, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
     {0, 4, mega_render_kernel<4, MEGA_BLOCK, false, false, FEAT_ALL>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_ALL, 2},
     {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_ALL>, STACK_SMEM(256), 256, FEAT_ALL, 2},
@@ -604,15 +707,16 @@ static const MegaVariant mega_variants[] = {
     /* LEAN instantiations: the same kernels without the code of what a scene does not contain.  FEATS = 0: spheres
      * with solid-colour lambertian / metal / dielectric / emissive materials (scene 0, Book 1 final); quads + instances
      * + light sampling, no media, no textures (the Cornell box). */
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, 0, 2, false, true>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
     {0, 10, mega_render_kernel<10, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
     {0, 12, mega_render_kernel<12, MEGA_BLOCK, false, false, 0>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, 0, 2},
     {-1, 4, mega_render_kernel<4, 256, true, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>, STACK_SMEM(256), 256,
      FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS>,
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2, true, true>,
      STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_QUADS | FEAT_INSTANCES | FEAT_LIGHTS, 2},
     /* sphere-only worlds with an oversized primitive tested before the walk (FEAT_PRE): lean, and with everything */
-    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_PRE>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_PRE, 2},
+    {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_PRE, 2, false, true>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK, FEAT_PRE,
+     2},
     {0, 8, mega_render_kernel<8, MEGA_BLOCK, false, false, FEAT_ALL | FEAT_PRE>, STACK_SMEM(MEGA_BLOCK), MEGA_BLOCK,
      FEAT_ALL | FEAT_PRE, 2},
     /* the three default shapes again, walking the 4-wide tree */

@@ -245,6 +245,36 @@ def test_all_megakernel_variants_agree_bit_for_bit(rtc, gpu_scene, scene_id, mon
     scene.close()
 
 
+def test_warp_item_pool_renders_the_same_bits_as_per_lane_draws(rtc, gpu_scene, monkeypatch):
+    """The lean sphere kernel exists with the warp item pool (RT_MEGA_MINB=8: a warp draws the 32 items of a tile's
+    chunk and hands them to its lanes) and with one draw per lane (RT_MEGA_MINB=10, 12): who renders which item
+    changes, what an item sums does not -- identical radiance bits, counters and 8-bit frames; on a frame whose
+    width is not a multiple of the tile (padding items) and with few and with many chunks."""
+    monkeypatch.setenv("RT_BVH_PRE", "0")  # the kernels without the pre-walk primitives: FEATS = 0 in all three builds
+    sess, desc, _ = gpu_scene(1, 101, 24)
+    scene = rtc.Scene(desc)
+    monkeypatch.delenv("RT_BVH_PRE")
+    opts = rtc.make_opts(kernel="mega", rng="sample")
+    monkeypatch.setenv("RT_MEGA_NV", "0")
+    try:
+        for chunks in ("1", "2", "0"):  # 0: the guided plan (many items of falling size)
+            if chunks == "0":
+                monkeypatch.delenv("RT_MEGA_CHUNKS")
+            else:
+                monkeypatch.setenv("RT_MEGA_CHUNKS", chunks)
+            monkeypatch.setenv("RT_MEGA_MINB", "8")
+            rgb_p, rad_p, st_p = scene.render(sess.camera, opts)
+            assert st_p["samples"] == sess.width * sess.height * 24
+            for minb in ("10", "12"):
+                monkeypatch.setenv("RT_MEGA_MINB", minb)
+                rgb, rad, st = scene.render(sess.camera, opts)
+                assert same_bits(rad, rad_p).all(), (chunks, minb)
+                assert np.array_equal(rgb, rgb_p)
+                assert st["segments"] == st_p["segments"] and st["samples"] == st_p["samples"]
+    finally:
+        scene.close()
+
+
 @pytest.mark.parametrize("scene_id", [0, 1, 4, 5, 6, 7])
 def test_scene_build_options_agree_bit_for_bit(rtc, scene_factory, scene_id, monkeypatch):
     """Box leaves (six quads of a Box_new list in one leaf) against one leaf per quad, the one-quad-light fast path

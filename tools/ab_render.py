@@ -7,6 +7,7 @@ carries the tuning knobs RT_MEGA_*).  Prints one JSON line per frame: Mseg/s fro
 from __future__ import annotations
 
 import argparse
+import hashlib
 import importlib
 import json
 import os
@@ -33,7 +34,8 @@ def main():
         sess = rtc.Session(scene_id, width=width, spp=spp, depth=args.depth, aspect=aspect)
         scene = rtc.Scene(sess.flatten())
         opts = rtc.make_opts(kernel=args.kernel, rng="sample")
-        scene.render(sess.camera, opts, want_radiance=False)
+        rgb8, _, _ = scene.render(sess.camera, opts, want_radiance=False)
+        sha = hashlib.sha256(rgb8.tobytes()).hexdigest()[:16]  # A/B builds must render the same frame
         best, seg = 1e30, 0
         for _ in range(args.reps):
             _, _, st = scene.render(sess.camera, opts, want_radiance=False)
@@ -41,7 +43,7 @@ def main():
         scene.close()
         knobs = {k: v for k, v in os.environ.items() if k.startswith("RT_MEGA")}
         print(json.dumps({"tag": args.tag, "knobs": knobs, "scene": scene_id, "frame": [sess.width, sess.height],
-                          "spp": spp, "depth": args.depth, "segments": seg, "kernel_ms": best, "mseg_per_s": seg / best * 1e-3}), flush=True)
+                          "spp": spp, "depth": args.depth, "sha": sha, "segments": seg, "kernel_ms": best, "mseg_per_s": seg / best * 1e-3}), flush=True)
 
 
 if __name__ == "__main__":
