@@ -65,6 +65,11 @@ RTC_DEV Frame frame_of(const DScene &sc, const RenderJob &job, const MegaPlan &p
   return f;
 }
 
+#ifdef RTC_TIMELINE
+#define TL_MAX_WARPS 16384
+__device__ unsigned long long tl_records[TL_MAX_WARPS][8];
+#endif
+
 /* A word of per-lane state: a register, or (COLD) one slot of shared memory -- for what no traversal touches (the
  * sample sums of the work item, the launch counters), so that the node loop has the registers to itself. */
 template <bool COLD, typename T> struct Kept {
@@ -234,8 +239,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   __shared__ unsigned cold_u[COLD ? 4 : 1][COLD ? BLOCK : 1];
   __shared__ float cold_f[COLD ? 3 : 1][COLD ? BLOCK : 1];
   const int cold_t = COLD ? (int)threadIdx.x : 0;
-  /* POOL: the warp's drawn and not yet handed-out items [next, end) */
-  __shared__ volatile unsigned pool_w[2][POOL ? BLOCK / 32 : 1];
+  /* POOL: the warp's drawn and not yet handed-out items [next, end), and their chunk and tile */
+  __shared__ volatile unsigned pool_w[5][POOL ? BLOCK / 32 : 1];
   if (POOL) {
     if ((threadIdx.x & 31u) == 0)
       pool_w[0][threadIdx.x >> 5] = pool_w[1][threadIdx.x >> 5] = 0;
@@ -245,7 +250,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       n_samples(&cold_u[COLD ? 2 : 0][cold_t]), n_nan(&cold_u[COLD ? 3 : 0][cold_t]);
   Kept<COLD, float> sum_x(&cold_f[0][cold_t]), sum_y(&cold_f[COLD ? 1 : 0][cold_t]), sum_z(&cold_f[COLD ? 2 : 0][cold_t]);
 #ifdef RTC_TIMELINE /* development build: when does every CTA start, run out of items, and end? */
-  unsigned long long tl_in = 0, tl_dry = 0;
+  unsigned long long tl_in = 0, tl_dry = 0, tl_last = 0; /* tl_last: the warp's last draw from the queue (POOL) */
+  unsigned tl_last_chunk = 0, tl_draws = 0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_in));
 #endif
 
@@ -295,6 +301,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
       unsigned need_mask = __ballot_sync(0xffffffffu, need);
       while (need_mask) {
         unsigned next = pool_w[0][warp_id], end = pool_w[1][warp_id];
+        /* the batch is one chunk of one tile: decoded once per draw, not once per item */
+        int batch_chunk = (int)pool_w[2][warp_id], batch_x = (int)pool_w[3][warp_id], batch_y = (int)pool_w[4][warp_id];
         if (next == end) {
           unsigned base = 0;
           if (lane_id == 0)
@@ -303,16 +311,27 @@ __global__ void __launch_bounds__(BLOCK, MINB)
           if (base >= f.n_items) { /* n_items is a multiple of 32: nothing left for anybody */
             if (need)
               done = true;
+#ifdef RTC_TIMELINE
+            if (tl_dry == 0)
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_dry));
+#endif
             break;
           }
           next = base, end = base + 32u;
+          const unsigned c = base / (f.tiles * 32u);
+          batch_chunk = (int)c;
+          item_to_pixel(base - c * (f.tiles * 32u), f.w, f.h, batch_x, batch_y); /* the tile's first pixel */
+#ifdef RTC_TIMELINE
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_last));
+          tl_last_chunk = c, tl_draws++;
+#endif
         }
         const unsigned rank = __popc(need_mask & ((1u << lane_id) - 1u));
         if (need && rank < end - next) {
-          const unsigned item = next + rank, c = item / (f.tiles * 32u), pix = item - c * (f.tiles * 32u);
-          item_to_pixel(pix, f.w, f.h, pi, pj);
+          const unsigned k = (next + rank) & 31u; /* 8x4 tile, row-major (item_to_pixel) */
+          pi = batch_x + (int)(k & 7u), pj = batch_y + (int)(k >> 3);
           if (pi < f.w && pj < f.h) { /* else: padding of the last tile column / row, the lane asks again */
-            chunk_id = (int)c;
+            chunk_id = batch_chunk;
             s = job.sample_begin + plan_chunk_begin(plan, chunk_id);
             sum_x.set(0.0f), sum_y.set(0.0f), sum_z.set(0.0f);
             if (job.rng_mode == RT_RNG_PIXEL)
@@ -322,8 +341,10 @@ __global__ void __launch_bounds__(BLOCK, MINB)
         }
         next += min(end - next, (unsigned)__popc(need_mask));
         __syncwarp();
-        if (lane_id == 0)
+        if (lane_id == 0) {
           pool_w[0][warp_id] = next, pool_w[1][warp_id] = end;
+          pool_w[2][warp_id] = (unsigned)batch_chunk, pool_w[3][warp_id] = (unsigned)batch_x, pool_w[4][warp_id] = (unsigned)batch_y;
+        }
         __syncwarp();
         need_mask = __ballot_sync(0xffffffffu, need);
       }
@@ -447,10 +468,17 @@ __global__ void __launch_bounds__(BLOCK, MINB)
   /* a lane that ran out of items while holding a finished chunk already stored it in phase 1 */
   flush_counters(job, n_segments.get(), n_pdf.get(), n_samples.get(), n_nan.get());
 #ifdef RTC_TIMELINE
-  if (threadIdx.x == 0) {
+  if ((threadIdx.x & 31u) == 0) { /* one line per warp */
     unsigned long long tl_out;
+    unsigned smid;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_out));
-    printf("TL %u %llu %llu %llu %u\n", blockIdx.x, tl_in, tl_dry, tl_out, trip);
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    /* into a device array the host prints after the launch (printf from 4 736 warps stretches the kernel by ms) */
+    const unsigned w = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
+    if (w < TL_MAX_WARPS) {
+      unsigned long long *r = tl_records[w];
+      r[0] = tl_in, r[1] = tl_dry, r[2] = tl_out, r[3] = trip, r[4] = tl_last, r[5] = tl_last_chunk, r[6] = tl_draws, r[7] = smid;
+    }
   }
 #endif
 }
@@ -894,6 +922,19 @@ cudaError_t mega_render(const DScene &sc, const RenderJob &job, const MegaPlan &
   *launches = 1;
   if (err != cudaSuccess)
     return err;
+#ifdef RTC_TIMELINE
+  {
+    static unsigned long long host_records[TL_MAX_WARPS][8];
+    cudaStreamSynchronize(stream);
+    cudaMemcpyFromSymbol(host_records, tl_records, sizeof(host_records));
+    const unsigned n_warps = plan.blocks * (plan.threads / 32);
+    for (unsigned w = 0; w < n_warps && w < TL_MAX_WARPS; w++) {
+      const unsigned long long *r = host_records[w];
+      printf("TL %u %llu %llu %llu %llu %llu %llu %llu %llu\n", w, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7]);
+    }
+    fflush(stdout);
+  }
+#endif
   if (plan.n_chunks > 1) {
     size_t n_values = (size_t)job.cam.img_width * job.cam.img_height * 3;
     unsigned blocks = (unsigned)((n_values + 255) / 256);
